@@ -1,0 +1,128 @@
+/* uwie.h — C ABI of the B200-native enhance + score hot path.
+ *
+ * The reference (submarine0418/underwater_image_enhancement) is pure Python and has no FFI layer;
+ * its boundary for this path is the static-method API
+ *     six_stadigy.py:22-323        EnhancementStrategies.strategy1..6, detect_image_type, color_correction
+ *     enhancement_strategies.py:13-508   EnhancementStrategies.apply_strategy(img, name, params)
+ *     quality_assessment.py:215-286      QualityAssessment.comprehensive_assessment(img, weights)
+ *     main.py:116-155              per-image loop: every strategy, score each, keep the first maximum
+ *     six_stadigy.py:392-447       per-image loop: colour cast, six strategies, write all six
+ * The entry points below are what a ctypes binding of those loops calls (INTEGRATION.md shows the
+ * stubs).  Conventions: plain pointers and sizes only; `*_dev` pointers are CUDA device memory,
+ * `*_host` pointers are host memory; every call returns 0 on success or a negative uwie_status;
+ * nothing throws across the boundary; device entry points are asynchronous on `stream` (pass the
+ * cudaStream_t as a void*; NULL is the default stream) and never synchronise; there is NO CPU
+ * implementation behind this header — without a CUDA device every compute call fails with
+ * UWIE_ERR_CUDA.
+ */
+#ifndef UWIE_H
+#define UWIE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UWIE_VERSION 100          /* 0.1.0 */
+#define UWIE_MAX_STRATEGIES 6
+#define UWIE_SCORE_COLS 9         /* total, contrast, sharpness, entropy, saturation, brightness,
+                                     edge_density, colorfulness, naturalness (QA:243-281 order) */
+
+typedef enum {
+    UWIE_OK = 0,
+    UWIE_ERR_ARG = -1,            /* bad argument (the Python shims raise ValueError) */
+    UWIE_ERR_CUDA = -2,           /* CUDA runtime error, see uwie_last_error() */
+    UWIE_ERR_NOMEM = -3,
+    UWIE_ERR_SELECT = -4          /* exact percentile selection overflowed its candidate buffer */
+} uwie_status;
+
+/* The two strategy libraries of the reference, as presets. */
+typedef enum {
+    UWIE_LIB_SIX = 0,             /* six_stadigy.py: colour cast + strategy1..6, float32 buffers */
+    UWIE_LIB_ES = 1               /* enhancement_strategies.py + config.py:28-75, float64 buffers */
+} uwie_library_id;
+
+/* One strategy, as data (see csrc/uwie_recipe.h for the chain it describes). */
+typedef struct {
+    int dehaze;                   /* quadtree light + transmission + guided filter + recover */
+    double omega;
+    int radius;
+    double eps;
+    int n_pre;                    /* percentile stretches before the histogram stage (<= 2) */
+    double pre_lo[2], pre_hi[2];
+    int equalize;                 /* per-channel cv2.equalizeHist (ES:331-345) */
+    int clahe;                    /* CLAHE on the 8-bit Lab L plane */
+    double clip_limit;
+    int tiles_x, tiles_y;
+    int n_post;                   /* percentile stretches after CLAHE / equalizeHist (<= 2) */
+    double post_lo[2], post_hi[2];
+    int gamma_on;
+    double gamma;                 /* the reference's gamma argument (SS: x**gamma, ES: x**(1/gamma)) */
+} uwie_strategy;
+
+typedef struct {
+    int f64;                      /* float type of the image buffers: 0 float32 (SS), 1 float64 (ES) */
+    int colour_cast;              /* detect_image_type + color_correction first (SS:292-323) */
+    double dark_guard;            /* 1e-6 (SS:170) / 1e-10 (ES:221) */
+    int clip_t0;                  /* clip raw transmission to [.1,1] before the guided filter (SS:174) */
+    double stretch_guard;         /* 1e-6 (SS:198) / 1e-10 (ES:268) */
+    int gamma_inverse;            /* 1: exponent is 1/gamma and the result is clipped (ES:284-285) */
+    double weights[8];            /* comprehensive_assessment weights, QA key order */
+} uwie_library;
+
+typedef struct uwie_engine uwie_engine;
+
+int uwie_version(void);
+const char* uwie_last_error(void);
+
+/* Fill `lib` and `strategies` (room for UWIE_MAX_STRATEGIES) with a preset; returns the count. */
+int uwie_preset(int library_id, uwie_library* lib, uwie_strategy* strategies);
+
+/* Device memory an engine needs for `max_batch` frames of H x W (0 on bad arguments). */
+size_t uwie_workspace_bytes(const uwie_library* lib, const uwie_strategy* strategies, int n_strategies,
+                            int max_batch, int height, int width);
+
+/* Create an engine.  `workspace_dev` may be NULL (the engine allocates with cudaMalloc and owns
+ * it) or caller-owned device memory of at least uwie_workspace_bytes(...). */
+int uwie_engine_create(uwie_engine** out, const uwie_library* lib, const uwie_strategy* strategies,
+                       int n_strategies, int max_batch, int height, int width,
+                       void* workspace_dev, size_t workspace_bytes);
+void uwie_engine_destroy(uwie_engine* e);
+
+/* Enhance + score `batch` (<= max_batch) uint8 RGB frames [batch][H][W][3] resident on the device.
+ * Any output pointer may be NULL.
+ *   out_all_dev   uint8  [batch][S][H][W][3]   every strategy's output       (SS:430-447)
+ *   out_best_dev  uint8  [batch][H][W][3]      the selected strategy's output (main.py:150-155)
+ *   scores_dev    double [batch][S][9]         total + 8 sub-scores          (QA:215-286)
+ *   best_dev      int32  [batch]               first maximum of the totals   (main.py:144-146)
+ *   type_dev      int32  [batch]               0 normal / 1 greenish / 2 bluish (SS:292-302)
+ *   light_dev     float  [batch][3]            atmospheric light             (ES:77-144, SS:48-113)
+ * Asynchronous on `stream`. */
+int uwie_enhance_score(uwie_engine* e, const uint8_t* frames_dev, int batch,
+                       uint8_t* out_all_dev, uint8_t* out_best_dev, double* scores_dev,
+                       int32_t* best_dev, int32_t* type_dev, float* light_dev, void* stream);
+
+/* Same call with HOST buffers (any count of frames, processed in chunks of max_batch): copies the
+ * frames to the device, runs, copies the requested results back, synchronises.  Pinned host
+ * memory makes the copies asynchronous with respect to the kernels of the neighbouring chunk. */
+int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int count,
+                            uint8_t* out_all_host, uint8_t* out_best_host, double* scores_host,
+                            int32_t* best_host, int32_t* type_host, float* light_host, void* stream);
+
+/* Sticky device-side status of the engine (synchronises `stream`): 0 or a negative uwie_status. */
+int uwie_engine_check(uwie_engine* e, void* stream);
+
+/* Kernels launched by the last uwie_enhance_score call on this engine. */
+int uwie_engine_last_launches(const uwie_engine* e);
+
+/* Test hook: device pointer and byte size of a named intermediate of the last run
+ * ("frame_hist", "cast", "tables", "rects", "q_trace", "quad_counts", "light", "ab", "recovered",
+ *  "tile_lut", "out_hist", "gray", "qa", "edge_counts", "targets").  NULL if unknown. */
+const void* uwie_engine_debug(const uwie_engine* e, const char* name, size_t* bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UWIE_H */

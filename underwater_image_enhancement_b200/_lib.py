@@ -1,0 +1,91 @@
+"""ctypes binding of include/uwie.h.  Fails loudly when the native library is missing: there is no
+Python or CPU fallback for the hot path."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libuwie_b200.so")
+
+MAX_STRATEGIES = 6
+SCORE_COLS = 9
+LIB_SIX, LIB_ES = 0, 1
+OK, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_SELECT = 0, -1, -2, -3, -4
+
+# every symbol include/uwie.h declares (tests check that the library exports all of them)
+EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_bytes", "uwie_engine_create",
+           "uwie_engine_destroy", "uwie_enhance_score", "uwie_enhance_score_host", "uwie_engine_check",
+           "uwie_engine_last_launches", "uwie_engine_debug")
+
+
+class Strategy(C.Structure):
+    _fields_ = [("dehaze", C.c_int), ("omega", C.c_double), ("radius", C.c_int), ("eps", C.c_double),
+                ("n_pre", C.c_int), ("pre_lo", C.c_double * 2), ("pre_hi", C.c_double * 2),
+                ("equalize", C.c_int), ("clahe", C.c_int), ("clip_limit", C.c_double),
+                ("tiles_x", C.c_int), ("tiles_y", C.c_int),
+                ("n_post", C.c_int), ("post_lo", C.c_double * 2), ("post_hi", C.c_double * 2),
+                ("gamma_on", C.c_int), ("gamma", C.c_double)]
+
+
+class Library(C.Structure):
+    _fields_ = [("f64", C.c_int), ("colour_cast", C.c_int), ("dark_guard", C.c_double),
+                ("clip_t0", C.c_int), ("stretch_guard", C.c_double), ("gamma_inverse", C.c_int),
+                ("weights", C.c_double * 8)]
+
+
+class UwieError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"uwie error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m underwater_image_enhancement_b200.build` "
+            "(nvcc, sm_100a).  The hot path has no CPU or pure-Python fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.uwie_version.restype = C.c_int
+    lib.uwie_last_error.restype = C.c_char_p
+    lib.uwie_preset.argtypes = [C.c_int, C.POINTER(Library), C.POINTER(Strategy)]
+    lib.uwie_preset.restype = C.c_int
+    lib.uwie_workspace_bytes.argtypes = [C.POINTER(Library), C.POINTER(Strategy), C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.uwie_workspace_bytes.restype = C.c_size_t
+    lib.uwie_engine_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(Library), C.POINTER(Strategy), C.c_int,
+                                       C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t]
+    lib.uwie_engine_create.restype = C.c_int
+    lib.uwie_engine_destroy.argtypes = [C.c_void_p]
+    lib.uwie_engine_destroy.restype = None
+    lib.uwie_enhance_score.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7
+    lib.uwie_enhance_score.restype = C.c_int
+    lib.uwie_enhance_score_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7
+    lib.uwie_enhance_score_host.restype = C.c_int
+    lib.uwie_engine_check.argtypes = [C.c_void_p, C.c_void_p]
+    lib.uwie_engine_check.restype = C.c_int
+    lib.uwie_engine_last_launches.argtypes = [C.c_void_p]
+    lib.uwie_engine_last_launches.restype = C.c_int
+    lib.uwie_engine_debug.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_size_t)]
+    lib.uwie_engine_debug.restype = C.c_void_p
+    _lib = lib
+    return lib
+
+
+def check(code: int) -> None:
+    if code != 0:
+        raise UwieError(code, load().uwie_last_error().decode("utf-8", "replace"))
+
+
+def preset(library_id: int):
+    lib = Library()
+    arr = (Strategy * MAX_STRATEGIES)()
+    n = load().uwie_preset(library_id, C.byref(lib), arr)
+    if n < 0:
+        check(n)
+    return lib, [arr[i] for i in range(n)]

@@ -1,0 +1,157 @@
+// Launch wrappers of the kernel files (internal; the public boundary is include/uwie.h).
+// Every wrapper enqueues on `st`, never synchronises, and returns the number of kernels launched.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "k_common.cuh"
+#include "uwie_recipe.h"
+
+namespace uwie {
+
+// ------------------------------------------------------------------ k_canny.cu
+enum { CANNY_QUADRANTS = 0, CANNY_PLANES = 1 };
+struct CannyArgs {
+    int mode;
+    int H, W;
+    int low, high;
+    // CANNY_QUADRANTS: instance = frame * 4 + quadrant of rects[frame]; gray is computed from the
+    // frame bytes through the colour-cast byte table; per-quadrant channel histograms are produced.
+    const uint8_t* frames;      // [B][H][W][3]
+    const CastTables* cast;     // [B]
+    const QuadRect* rects;      // [B]
+    int level;
+    unsigned* quad_hist;        // [B][kQuadLevelsMax][4][3][256]
+    // CANNY_PLANES: instance = one gray plane
+    const uint8_t* gray;        // [instances][H][W]
+    int planes_per_img;
+    // scratch + result
+    uint8_t* map;               // [planes][H][W]   0 / 1 weak / 2 strong
+    int* labels;                // [planes][H][W]
+    unsigned* counts;           // QUADRANTS: [B][kQuadLevelsMax][4]; PLANES: [instances]
+};
+int launch_canny(const CannyArgs& a, int max_rows, int max_cols, int instances, cudaStream_t st);
+
+// ------------------------------------------------------------------ k_stats.cu
+// per-channel 256-bin histograms of uint8 HWC frames: hist[B][3][256] (must be zeroed)
+int launch_frame_hist(const uint8_t* frames, int B, int H, int W, unsigned* hist, cudaStream_t st);
+
+// ------------------------------------------------------------------ k_quadtree.cu
+struct QuadArgs {
+    int B, H, W;
+    const uint8_t* frames;
+    const CastTables* cast;
+    QuadRect* rects;
+    const unsigned* quad_hist;   // [B][L][4][3][256]
+    const unsigned* counts;      // [B][L][4]
+    double* q_trace;             // [B][L][4]  Q of every visited quadrant (diagnostics / tests)
+    float* light;                // [B][3]
+};
+int launch_quad_init(const QuadArgs& a, cudaStream_t st);
+int launch_quad_descend(const QuadArgs& a, int level, cudaStream_t st);
+int launch_quad_brightest(const QuadArgs& a, cudaStream_t st);
+
+// ------------------------------------------------------------------ k_setup.cu
+// Per (frame, strategy) tables.  Values are stored as double but always hold numbers of the
+// library's float type (float32 values are exact in double).
+struct StratTables {
+    uint8_t preq[3][256];     // no-dehaze strategies: byte entering CLAHE, by frame byte
+    double postf[3][256];     // final float value, by CLAHE-output byte (or by frame byte if no CLAHE)
+    uint8_t postq[3][256];    // its truncation to a byte
+    double st_lo[kMaxStretch][3];   // dehaze strategies: float-domain stretches  (x - lo) / den
+    double st_den[kMaxStretch][3];
+};
+struct SetupArgs {
+    int B, S;
+    long long n;                 // pixels per frame
+    Library lib;
+    const Recipe* recipes;       // [S] device
+    const unsigned* frame_hist;  // [B][3][256]
+    const unsigned* out_hist;    // [B][S][3][256] histograms of the CLAHE output (post-stretch strategies)
+    int* types;                  // [B]
+    CastTables* cast;            // [B]
+    StratTables* tables;         // [B][S]
+};
+int launch_setup_cast(const SetupArgs& a, cudaStream_t st);
+int launch_setup_frame_luts(const SetupArgs& a, cudaStream_t st);
+int launch_setup_post_luts(const SetupArgs& a, cudaStream_t st);
+
+// ------------------------------------------------------------------ k_guided.cu / k_select.cu
+enum { UWIE_STATUS_SELECT_OVERFLOW = 1, UWIE_STATUS_SELECT_INTERNAL = 2 };
+struct GuidedArgs {
+    int B, S, H, W;
+    Library lib;
+    const Recipe* recipes;       // [S] device
+    int n_dehaze;                // number of dehaze strategies
+    int dehaze_idx[kStrategiesMax];   // their strategy indices
+    int rows_per_block;
+    const uint8_t* frames;
+    const CastTables* cast;
+    const float* light;          // [B][3]
+    double* ab;                  // [B * n_dehaze][2][H][W]
+    void* recovered;             // [B * n_dehaze][H][W][3] in the library's float type
+    unsigned* sel_hist_a;        // [B * n_dehaze][3][kSelBins]
+};
+int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st);
+
+struct SelTarget {
+    long long rank;   // rank still to resolve inside the current bin
+    int bin_a, bin_b;
+    int count;        // gathered candidates
+    int active;
+};
+struct SelectArgs {
+    int B, S;
+    long long n;
+    Library lib;
+    const Recipe* recipes;
+    int n_dehaze;
+    int dehaze_idx[kStrategiesMax];
+    const void* recovered;
+    const unsigned* sel_hist_a;  // [inst][3][kSelBins]
+    unsigned* sel_hist_b;        // [inst][kSelTargets][kSelSub]
+    SelTarget* targets;          // [inst][kSelTargets]
+    void* sel_buf;               // [inst][kSelTargets][kSelCap] in the library's float type
+    StratTables* tables;         // [B][S]
+    int* status;
+};
+int launch_select(const SelectArgs& a, cudaStream_t st);
+
+// ------------------------------------------------------------------ k_apply.cu / k_score.cu
+constexpr int kMaxTiles = 256;   // CLAHE tile grids up to 16 x 16
+struct ApplyArgs {
+    int B, S, H, W;
+    Library lib;
+    const Recipe* recipes;
+    int n_dehaze;
+    int dehaze_slot[kStrategiesMax];   // strategy -> slot in the recovered buffer, -1 if none
+    const uint8_t* frames;
+    const StratTables* tables;
+    const void* recovered;
+    const ColorTables* ctab;
+    uint8_t* tile_lut;           // [B][S][kMaxTiles][256]
+    unsigned* out_hist;          // [B][S][3][256]
+    uint8_t* out;                // [B][S][H][W][3]
+    uint8_t* gray;               // [B][S][H][W]
+    QaAccum* qa;                 // [B][S]
+    double* cf_part;             // [B][S][final_blocks][4]
+    int pix_per_block;
+    int final_blocks;
+};
+int launch_clahe_luts(const ApplyArgs& a, int max_tiles, cudaStream_t st);
+int launch_apply(const ApplyArgs& a, bool final_pass, cudaStream_t st);
+
+struct ScoreArgs {
+    int B, S;
+    long long n;
+    Library lib;
+    const QaAccum* qa;
+    const double* cf_part;
+    int final_blocks;
+    const unsigned* edge_counts; // [B][S]
+    double* scores;              // [B][S][kScoreCols]
+    int* best;                   // [B]
+};
+int launch_scores(const ScoreArgs& a, cudaStream_t st);
+
+}  // namespace uwie

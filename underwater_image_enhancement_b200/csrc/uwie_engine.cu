@@ -1,0 +1,546 @@
+// Engine: owns the workspace layout and enqueues the kernel sequence of one batch.
+// C ABI in include/uwie.h.  No CPU path: every entry point needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/uwie.h"
+#include "k_kernels.h"
+#include "uwie_tables.h"
+
+using namespace uwie;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t _e = (call);                                                          \
+        if (_e != cudaSuccess)                                                            \
+            return fail(UWIE_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
+
+struct Bump {
+    size_t off = 0;
+    size_t take(size_t bytes) {
+        const size_t at = off;
+        off += (bytes + 255) & ~(size_t)255;
+        return at;
+    }
+};
+
+struct Layout {
+    // zeroed every run (contiguous)
+    size_t zero_begin, frame_hist, quad_hist, quad_counts, sel_hist_a, sel_hist_b, out_hist, qa,
+        edge_counts, zero_end;
+    size_t recipes, ctab, status, types, cast, tables, rects, q_trace, light, map, labels, ab,
+        recovered, targets, sel_buf, tile_lut, out, gray, cf_part, scores, best;
+    size_t total;
+};
+
+}  // namespace
+
+struct uwie_engine {
+    Library lib;
+    std::vector<Recipe> recipes;
+    int S = 0, B = 0, H = 0, W = 0;
+    int n_dehaze = 0;
+    int dehaze_idx[kStrategiesMax];
+    int dehaze_slot[kStrategiesMax];
+    int max_radius = 0, max_tiles = 0;
+    bool need_hist_pass = false;
+    int final_blocks = 0, pix_per_block = 0;
+    std::vector<std::pair<int, int>> quad_dims;   // per level: max quadrant rows, cols
+    Layout L;
+    char* ws = nullptr;
+    bool owns_ws = false;
+    int last_launches = 0;
+    // pinned staging for the host entry point
+    uint8_t* pin_frames = nullptr;
+    template <class T> T* at(size_t off) const { return reinterpret_cast<T*>(ws + off); }
+};
+
+namespace {
+
+int build_recipes(const uwie_library* lib, const uwie_strategy* st, int n, int H, int W, Library* L,
+                  std::vector<Recipe>* out) {
+    if (!lib || !st || n < 1 || n > kStrategiesMax || H < 1 || W < 1) return fail(UWIE_ERR_ARG, "bad engine arguments");
+    std::memset(L, 0, sizeof(*L));
+    L->f64 = lib->f64 ? 1 : 0;
+    L->colour_cast = lib->colour_cast ? 1 : 0;
+    L->dark_guard = lib->dark_guard;
+    L->clip_t0 = lib->clip_t0 ? 1 : 0;
+    L->stretch_guard = lib->stretch_guard;
+    L->n_strategies = n;
+    for (int i = 0; i < 8; ++i) L->weights[i] = lib->weights[i];
+    const long long npix = (long long)H * W;
+    auto plan = [&](double pct) {
+        PercentilePlan p = L->f64 ? percentile_plan_f64(npix, pct) : percentile_plan_f32(npix, pct);
+        RankPlan r; r.k = p.k; r.gamma = p.gamma; return r;
+    };
+    out->clear();
+    for (int i = 0; i < n; ++i) {
+        const uwie_strategy& s = st[i];
+        Recipe r;
+        std::memset(&r, 0, sizeof(r));
+        if (s.n_pre < 0 || s.n_pre > kMaxStretch || s.n_post < 0 || s.n_post > kMaxStretch)
+            return fail(UWIE_ERR_ARG, "at most two stretches before and after the histogram stage");
+        if (s.dehaze && (s.radius < 1 || s.radius > 64)) return fail(UWIE_ERR_ARG, "guided radius must be in [1, 64]");
+        if (s.dehaze && (s.equalize || s.n_post)) return fail(UWIE_ERR_ARG, "unsupported chain: dehaze + equalize/post-stretch");
+        if (s.clahe && s.equalize) return fail(UWIE_ERR_ARG, "unsupported chain: clahe + equalize");
+        if (!s.clahe && !s.equalize && !s.dehaze && s.n_post) return fail(UWIE_ERR_ARG, "post-stretch needs a histogram stage");
+        r.dehaze = s.dehaze ? 1 : 0;
+        r.omega = (float)s.omega;
+        r.radius = s.radius;
+        r.eps = s.eps;
+        r.n_pre = s.n_pre;
+        for (int k = 0; k < s.n_pre; ++k) { r.pre[k].lo = plan(s.pre_lo[k]); r.pre[k].hi = plan(s.pre_hi[k]); }
+        r.equalize = s.equalize ? 1 : 0;
+        r.clahe = s.clahe ? 1 : 0;
+        if (r.clahe) {
+            if (s.tiles_x < 1 || s.tiles_y < 1 || s.tiles_x * s.tiles_y > kMaxTiles)
+                return fail(UWIE_ERR_ARG, "CLAHE tile grid must have between 1 and 256 tiles");
+            r.tiles_x = s.tiles_x; r.tiles_y = s.tiles_y;
+            int tw, th;
+            if (W % r.tiles_x == 0 && H % r.tiles_y == 0) { tw = W / r.tiles_x; th = H / r.tiles_y; }
+            else { tw = (W + (r.tiles_x - W % r.tiles_x)) / r.tiles_x; th = (H + (r.tiles_y - H % r.tiles_y)) / r.tiles_y; }
+            r.clahe_clip = clahe_clip_count(s.clip_limit, tw * th);
+        }
+        r.n_post = s.n_post;
+        for (int k = 0; k < s.n_post; ++k) { r.post[k].lo = plan(s.post_lo[k]); r.post[k].hi = plan(s.post_hi[k]); }
+        r.gamma_on = s.gamma_on ? 1 : 0;
+        if (lib->gamma_inverse) { r.gamma_exp = 1.0 / s.gamma; r.gamma_clip = 1; }
+        else { r.gamma_exp = s.gamma; r.gamma_clip = 0; }
+        if (!L->f64) r.gamma_exp = (double)(float)r.gamma_exp;   // a Python float meets a float32 array
+        out->push_back(r);
+    }
+    return UWIE_OK;
+}
+
+void plan_layout(uwie_engine* e) {
+    Bump b;
+    Layout& L = e->L;
+    const size_t B = e->B, S = e->S, N = (size_t)e->H * e->W, nd = e->n_dehaze;
+    const size_t tsz = e->lib.f64 ? 8 : 4;
+    L.zero_begin = b.off;
+    L.frame_hist = b.take(B * 768 * 4);
+    L.quad_hist = b.take(nd ? B * kQuadLevelsMax * 4 * 768 * 4 : 0);
+    L.quad_counts = b.take(nd ? B * kQuadLevelsMax * 4 * 4 : 0);
+    L.sel_hist_a = b.take(B * nd * 3 * kSelBins * 4);
+    L.sel_hist_b = b.take(B * nd * kSelTargets * kSelSub * 4);
+    L.out_hist = b.take(B * S * 768 * 4);
+    L.qa = b.take(B * S * sizeof(QaAccum));
+    L.edge_counts = b.take(B * S * 4);
+    L.zero_end = b.off;
+    L.recipes = b.take(S * sizeof(Recipe));
+    L.ctab = b.take(sizeof(ColorTables));
+    L.status = b.take(256);
+    L.types = b.take(B * 4);
+    L.cast = b.take(B * sizeof(CastTables));
+    L.tables = b.take(B * S * sizeof(StratTables));
+    L.rects = b.take(B * sizeof(QuadRect));
+    L.q_trace = b.take(B * kQuadLevelsMax * 4 * 8);
+    L.light = b.take(B * 3 * 4);
+    L.map = b.take(B * S * N);
+    L.labels = b.take(B * S * N * 4);
+    L.ab = b.take(B * nd * 2 * N * 8);
+    L.recovered = b.take(B * nd * N * 3 * tsz);
+    L.targets = b.take(B * nd * kSelTargets * sizeof(SelTarget));
+    L.sel_buf = b.take(B * nd * kSelTargets * kSelCap * tsz);
+    L.tile_lut = b.take(e->max_tiles ? B * S * kMaxTiles * 256 : 0);
+    L.out = b.take(B * S * N * 3);
+    L.gray = b.take(B * S * N);
+    L.cf_part = b.take(B * S * (size_t)e->final_blocks * 4 * 8);
+    L.scores = b.take(B * S * kScoreCols * 8);
+    L.best = b.take(B * 4);
+    L.total = b.off;
+}
+
+int init_engine_shape(uwie_engine* e, const uwie_library* lib, const uwie_strategy* st, int n, int B, int H, int W) {
+    if (B < 1) return fail(UWIE_ERR_ARG, "max_batch must be positive");
+    if ((long long)H * W >= (1LL << 30)) return fail(UWIE_ERR_ARG, "frame too large");
+    int rc = build_recipes(lib, st, n, H, W, &e->lib, &e->recipes);
+    if (rc) return rc;
+    e->S = n; e->B = B; e->H = H; e->W = W;
+    e->n_dehaze = 0; e->max_radius = 0; e->max_tiles = 0; e->need_hist_pass = false;
+    for (int i = 0; i < kStrategiesMax; ++i) { e->dehaze_idx[i] = 0; e->dehaze_slot[i] = -1; }
+    for (int i = 0; i < n; ++i) {
+        const Recipe& r = e->recipes[i];
+        if (r.dehaze) {
+            e->dehaze_slot[i] = e->n_dehaze;
+            e->dehaze_idx[e->n_dehaze++] = i;
+            if (r.radius > e->max_radius) e->max_radius = r.radius;
+        }
+        if (r.clahe) {
+            if (r.tiles_x * r.tiles_y > e->max_tiles) e->max_tiles = r.tiles_x * r.tiles_y;
+            if (r.n_post > 0) e->need_hist_pass = true;
+        }
+    }
+    const size_t N = (size_t)H * W;
+    e->pix_per_block = 4096;
+    e->final_blocks = (int)((N + e->pix_per_block - 1) / e->pix_per_block);
+    // quadtree: upper bound of the quadrant size per level (ceil halves), enhancement_strategies.py:104-119
+    e->quad_dims.clear();
+    int rows = H, cols = W;
+    while (rows > 1 && cols > 1 && (int)e->quad_dims.size() < kQuadLevelsMax) {
+        rows = rows - rows / 2; cols = cols - cols / 2;
+        e->quad_dims.push_back({rows, cols});
+    }
+    plan_layout(e);
+    return UWIE_OK;
+}
+
+}  // namespace
+
+// =====================================================================================
+// C ABI
+// =====================================================================================
+extern "C" {
+
+int uwie_version(void) { return UWIE_VERSION; }
+const char* uwie_last_error(void) { return g_err.c_str(); }
+
+int uwie_preset(int library_id, uwie_library* lib, uwie_strategy* st) {
+    if (!lib || !st) return fail(UWIE_ERR_ARG, "null preset output");
+    std::memset(lib, 0, sizeof(*lib));
+    std::memset(st, 0, sizeof(uwie_strategy) * UWIE_MAX_STRATEGIES);
+    auto dehaze = [](uwie_strategy& s, double omega, int r, double eps) { s.dehaze = 1; s.omega = omega; s.radius = r; s.eps = eps; };
+    auto pre = [](uwie_strategy& s, double lo, double hi) { s.pre_lo[s.n_pre] = lo; s.pre_hi[s.n_pre] = hi; ++s.n_pre; };
+    auto post = [](uwie_strategy& s, double lo, double hi) { s.post_lo[s.n_post] = lo; s.post_hi[s.n_post] = hi; ++s.n_post; };
+    auto clahe = [](uwie_strategy& s, double clip) { s.clahe = 1; s.clip_limit = clip; s.tiles_x = 8; s.tiles_y = 8; };
+    auto gamma = [](uwie_strategy& s, double g) { s.gamma_on = 1; s.gamma = g; };
+    if (library_id == UWIE_LIB_SIX) {
+        // six_stadigy.py:230-285; white_balance(p) is the stretch (p, 100 - p) (SS:210-219)
+        lib->f64 = 0; lib->colour_cast = 1; lib->dark_guard = 1e-6; lib->clip_t0 = 1;
+        lib->stretch_guard = 1e-6; lib->gamma_inverse = 0;
+        const double w[8] = {0.20, 0.20, 0.15, 0.15, 0.10, 0.10, 0.05, 0.05};   // QA:229-238
+        std::memcpy(lib->weights, w, sizeof(w));
+        dehaze(st[0], 0.3, 20, 0.5); pre(st[0], 5, 98); clahe(st[0], 3.0); gamma(st[0], 1.5);
+        dehaze(st[1], 0.5, 15, 0.5); pre(st[1], 15, 95); clahe(st[1], 2.0);
+        dehaze(st[2], 0.7, 10, 0.1); pre(st[2], 20, 85); pre(st[2], 2, 98);
+        clahe(st[3], 4.0); post(st[3], 10, 95); post(st[3], 3, 97); gamma(st[3], 1.3);
+        pre(st[4], 2, 98); pre(st[4], 15, 90); clahe(st[4], 1.5); gamma(st[4], 1.2);
+        pre(st[5], 5, 98); clahe(st[5], 3.5); gamma(st[5], 1.4);
+        return 6;
+    }
+    if (library_id == UWIE_LIB_ES) {
+        // config.py:28-85 through enhancement_strategies.py:349-474 (eps stays at its 1e-3 default)
+        lib->f64 = 1; lib->colour_cast = 0; lib->dark_guard = 1e-10; lib->clip_t0 = 0;
+        lib->stretch_guard = 1e-10; lib->gamma_inverse = 1;
+        const double w[8] = {0.25, 0.20, 0.15, 0.15, 0.15, 0.10, 0.0, 0.0};     // config.py:78-85
+        std::memcpy(lib->weights, w, sizeof(w));
+        dehaze(st[0], 0.5, 15, 1e-3); pre(st[0], 10, 95); gamma(st[0], 1.2);
+        dehaze(st[1], 0.6, 20, 1e-3); pre(st[1], 15, 92); gamma(st[1], 1.2);
+        dehaze(st[2], 0.4, 10, 1e-3); pre(st[2], 15, 95);
+        clahe(st[3], 2.0); post(st[3], 20, 85);
+        st[4].equalize = 1; post(st[4], 10, 95);
+        return 5;
+    }
+    return fail(UWIE_ERR_ARG, "unknown library id");
+}
+
+size_t uwie_workspace_bytes(const uwie_library* lib, const uwie_strategy* st, int n, int B, int H, int W) {
+    uwie_engine tmp;
+    if (init_engine_shape(&tmp, lib, st, n, B, H, W)) return 0;
+    return tmp.L.total;
+}
+
+int uwie_engine_create(uwie_engine** out, const uwie_library* lib, const uwie_strategy* st, int n, int B,
+                       int H, int W, void* workspace_dev, size_t workspace_bytes) {
+    if (!out) return fail(UWIE_ERR_ARG, "null engine output");
+    *out = nullptr;
+    uwie_engine* e = new uwie_engine();
+    int rc = init_engine_shape(e, lib, st, n, B, H, W);
+    if (rc) { delete e; return rc; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+        delete e;
+        return fail(UWIE_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    }
+    if (workspace_dev) {
+        if (workspace_bytes < e->L.total) { delete e; return fail(UWIE_ERR_NOMEM, "workspace too small"); }
+        e->ws = static_cast<char*>(workspace_dev);
+    } else {
+        if (cudaMalloc(&e->ws, e->L.total) != cudaSuccess) {
+            cudaGetLastError();
+            delete e;
+            return fail(UWIE_ERR_NOMEM, "cudaMalloc of the workspace failed");
+        }
+        e->owns_ws = true;
+    }
+    ColorTables tabs;
+    build_color_tables(&tabs);
+    cudaError_t ce = cudaMemcpy(e->ws + e->L.ctab, &tabs, sizeof(tabs), cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemcpy(e->ws + e->L.recipes, e->recipes.data(), sizeof(Recipe) * e->S, cudaMemcpyHostToDevice);
+    if (ce == cudaSuccess) ce = cudaMemset(e->ws + e->L.status, 0, 256);
+    if (ce != cudaSuccess) {
+        std::string msg = std::string("engine upload: ") + cudaGetErrorString(ce);
+        uwie_engine_destroy(e);
+        return fail(UWIE_ERR_CUDA, msg);
+    }
+    *out = e;
+    return UWIE_OK;
+}
+
+void uwie_engine_destroy(uwie_engine* e) {
+    if (!e) return;
+    if (e->owns_ws && e->ws) cudaFree(e->ws);
+    if (e->pin_frames) cudaFreeHost(e->pin_frames);
+    delete e;
+}
+
+int uwie_engine_last_launches(const uwie_engine* e) { return e ? e->last_launches : 0; }
+
+}  // extern "C"
+
+// =====================================================================================
+// the kernel sequence of one batch
+// =====================================================================================
+namespace {
+
+__global__ void gather_best_kernel(const uint8_t* __restrict__ all, const int* __restrict__ best, int S,
+                                   size_t bytes_per_image, uint8_t* __restrict__ out) {
+    const int b = blockIdx.y;
+    const uint8_t* src = all + ((size_t)b * S + best[b]) * bytes_per_image;
+    uint8_t* dst = out + (size_t)b * bytes_per_image;
+    const size_t n16 = bytes_per_image / 16;
+    const bool vec = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+    if (vec) {
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x)
+            reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+        for (size_t i = n16 * 16 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < bytes_per_image;
+             i += (size_t)gridDim.x * blockDim.x)
+            dst[i] = src[i];
+    } else {
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < bytes_per_image; i += (size_t)gridDim.x * blockDim.x)
+            dst[i] = src[i];
+    }
+}
+
+int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out_all, uint8_t* out_best,
+                  double* scores, int32_t* best, int32_t* types, float* light, cudaStream_t st) {
+    const Layout& L = e->L;
+    const int S = e->S, H = e->H, W = e->W;
+    const size_t N = (size_t)H * W;
+    int launches = 0;
+    CU(cudaMemsetAsync(e->ws + L.zero_begin, 0, L.zero_end - L.zero_begin, st));
+
+    uint8_t* out_buf = out_all ? out_all : e->at<uint8_t>(L.out);
+
+    launches += launch_frame_hist(frames, batch, H, W, e->at<unsigned>(L.frame_hist), st);
+
+    SetupArgs sa;
+    sa.B = batch; sa.S = S; sa.n = (long long)N; sa.lib = e->lib;
+    sa.recipes = e->at<Recipe>(L.recipes);
+    sa.frame_hist = e->at<unsigned>(L.frame_hist);
+    sa.out_hist = e->at<unsigned>(L.out_hist);
+    sa.types = e->at<int>(L.types);
+    sa.cast = e->at<CastTables>(L.cast);
+    sa.tables = e->at<StratTables>(L.tables);
+    launches += launch_setup_cast(sa, st);
+    launches += launch_setup_frame_luts(sa, st);
+
+    if (e->n_dehaze > 0) {
+        QuadArgs qa;
+        qa.B = batch; qa.H = H; qa.W = W; qa.frames = frames; qa.cast = sa.cast;
+        qa.rects = e->at<QuadRect>(L.rects);
+        qa.quad_hist = e->at<unsigned>(L.quad_hist);
+        qa.counts = e->at<unsigned>(L.quad_counts);
+        qa.q_trace = e->at<double>(L.q_trace);
+        qa.light = e->at<float>(L.light);
+        launches += launch_quad_init(qa, st);
+        CannyArgs ca;
+        std::memset(&ca, 0, sizeof(ca));
+        ca.mode = CANNY_QUADRANTS; ca.H = H; ca.W = W; ca.low = 50; ca.high = 150;
+        ca.frames = frames; ca.cast = sa.cast; ca.rects = qa.rects;
+        ca.quad_hist = e->at<unsigned>(L.quad_hist);
+        ca.map = e->at<uint8_t>(L.map); ca.labels = e->at<int>(L.labels);
+        ca.counts = e->at<unsigned>(L.quad_counts);
+        for (size_t lv = 0; lv < e->quad_dims.size(); ++lv) {
+            ca.level = (int)lv;
+            launches += launch_canny(ca, e->quad_dims[lv].first, e->quad_dims[lv].second, batch * 4, st);
+            launches += launch_quad_descend(qa, (int)lv, st);
+        }
+        launches += launch_quad_brightest(qa, st);
+
+        GuidedArgs ga;
+        std::memset(&ga, 0, sizeof(ga));
+        ga.B = batch; ga.S = S; ga.H = H; ga.W = W; ga.lib = e->lib; ga.recipes = sa.recipes;
+        ga.n_dehaze = e->n_dehaze;
+        for (int i = 0; i < kStrategiesMax; ++i) ga.dehaze_idx[i] = e->dehaze_idx[i];
+        ga.rows_per_block = H >= 512 ? (H + 7) / 8 : (H >= 128 ? (H + 1) / 2 : H);
+        ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;
+        ga.ab = e->at<double>(L.ab); ga.recovered = e->at<void>(L.recovered);
+        ga.sel_hist_a = e->at<unsigned>(L.sel_hist_a);
+        launches += launch_guided(ga, e->max_radius, st);
+
+        SelectArgs se;
+        std::memset(&se, 0, sizeof(se));
+        se.B = batch; se.S = S; se.n = (long long)N; se.lib = e->lib; se.recipes = sa.recipes;
+        se.n_dehaze = e->n_dehaze;
+        for (int i = 0; i < kStrategiesMax; ++i) se.dehaze_idx[i] = e->dehaze_idx[i];
+        se.recovered = ga.recovered; se.sel_hist_a = ga.sel_hist_a;
+        se.sel_hist_b = e->at<unsigned>(L.sel_hist_b);
+        se.targets = e->at<SelTarget>(L.targets);
+        se.sel_buf = e->at<void>(L.sel_buf);
+        se.tables = sa.tables;
+        se.status = e->at<int>(L.status);
+        launches += launch_select(se, st);
+    }
+
+    ApplyArgs aa;
+    std::memset(&aa, 0, sizeof(aa));
+    aa.B = batch; aa.S = S; aa.H = H; aa.W = W; aa.lib = e->lib; aa.recipes = sa.recipes;
+    aa.n_dehaze = e->n_dehaze;
+    for (int i = 0; i < kStrategiesMax; ++i) aa.dehaze_slot[i] = e->dehaze_slot[i];
+    aa.frames = frames; aa.tables = sa.tables; aa.recovered = e->at<void>(L.recovered);
+    aa.ctab = e->at<ColorTables>(L.ctab);
+    aa.tile_lut = e->at<uint8_t>(L.tile_lut);
+    aa.out_hist = e->at<unsigned>(L.out_hist);
+    aa.out = out_buf; aa.gray = e->at<uint8_t>(L.gray);
+    aa.qa = e->at<QaAccum>(L.qa); aa.cf_part = e->at<double>(L.cf_part);
+    aa.pix_per_block = e->pix_per_block; aa.final_blocks = e->final_blocks;
+    launches += launch_clahe_luts(aa, e->max_tiles, st);
+    if (e->need_hist_pass) {
+        launches += launch_apply(aa, false, st);
+        launches += launch_setup_post_luts(sa, st);
+    }
+    launches += launch_apply(aa, true, st);
+
+    CannyArgs cq;
+    std::memset(&cq, 0, sizeof(cq));
+    cq.mode = CANNY_PLANES; cq.H = H; cq.W = W; cq.low = 50; cq.high = 150;
+    cq.gray = aa.gray; cq.planes_per_img = S;
+    cq.map = e->at<uint8_t>(L.map); cq.labels = e->at<int>(L.labels);
+    cq.counts = e->at<unsigned>(L.edge_counts);
+    launches += launch_canny(cq, H, W, batch * S, st);
+
+    ScoreArgs sc;
+    sc.B = batch; sc.S = S; sc.n = (long long)N; sc.lib = e->lib;
+    sc.qa = aa.qa; sc.cf_part = aa.cf_part; sc.final_blocks = e->final_blocks;
+    sc.edge_counts = e->at<unsigned>(L.edge_counts);
+    sc.scores = e->at<double>(L.scores); sc.best = e->at<int>(L.best);
+    launches += launch_scores(sc, st);
+
+    if (out_best) {
+        gather_best_kernel<<<dim3(64, batch), 256, 0, st>>>(out_buf, sc.best, S, N * 3, out_best);
+        ++launches;
+    }
+    if (scores) CU(cudaMemcpyAsync(scores, sc.scores, sizeof(double) * batch * S * kScoreCols, cudaMemcpyDeviceToDevice, st));
+    if (best) CU(cudaMemcpyAsync(best, sc.best, sizeof(int) * batch, cudaMemcpyDeviceToDevice, st));
+    if (types) CU(cudaMemcpyAsync(types, sa.types, sizeof(int) * batch, cudaMemcpyDeviceToDevice, st));
+    if (light) CU(cudaMemcpyAsync(light, e->at<float>(L.light), sizeof(float) * batch * 3, cudaMemcpyDeviceToDevice, st));
+    CU(cudaGetLastError());
+    e->last_launches = launches;
+    return UWIE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int uwie_enhance_score(uwie_engine* e, const uint8_t* frames_dev, int batch, uint8_t* out_all_dev,
+                       uint8_t* out_best_dev, double* scores_dev, int32_t* best_dev, int32_t* type_dev,
+                       float* light_dev, void* stream) {
+    if (!e || !frames_dev) return fail(UWIE_ERR_ARG, "null engine or frames");
+    if (batch < 1 || batch > e->B) return fail(UWIE_ERR_ARG, "batch must be in [1, max_batch]");
+    return enqueue_batch(e, frames_dev, batch, out_all_dev, out_best_dev, scores_dev, best_dev, type_dev,
+                         light_dev, static_cast<cudaStream_t>(stream));
+}
+
+int uwie_engine_check(uwie_engine* e, void* stream) {
+    if (!e) return fail(UWIE_ERR_ARG, "null engine");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int status = 0;
+    CU(cudaMemcpyAsync(&status, e->ws + e->L.status, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (status) {
+        char buf[128];
+        std::snprintf(buf, sizeof(buf), "percentile selection failed on the device (status bits %d)", status);
+        return fail(UWIE_ERR_SELECT, buf);
+    }
+    return UWIE_OK;
+}
+
+int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int count, uint8_t* out_all_host,
+                            uint8_t* out_best_host, double* scores_host, int32_t* best_host,
+                            int32_t* type_host, float* light_host, void* stream) {
+    if (!e || !frames_host) return fail(UWIE_ERR_ARG, "null engine or frames");
+    if (count < 1) return fail(UWIE_ERR_ARG, "count must be positive");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t N = (size_t)e->H * e->W, S = e->S;
+    // device-side staging, allocated on first use and kept
+    if (!e->pin_frames) {
+        // layout: frames | out_best | types | light   (scores, best and out_all live in the workspace)
+        const size_t bytes = (size_t)e->B * (N * 3 * 2 + 4 + 12) + 1024;
+        void* p = nullptr;
+        CU(cudaMalloc(&p, bytes));
+        e->pin_frames = static_cast<uint8_t*>(p);
+    }
+    uint8_t* d_frames = e->pin_frames;
+    uint8_t* d_best_img = d_frames + (size_t)e->B * N * 3;
+    int32_t* d_types = reinterpret_cast<int32_t*>(d_best_img + (size_t)e->B * N * 3);
+    float* d_light = reinterpret_cast<float*>(d_types + e->B);
+    for (int done = 0; done < count; done += e->B) {
+        const int nb = count - done < e->B ? count - done : e->B;
+        CU(cudaMemcpyAsync(d_frames, frames_host + (size_t)done * N * 3, (size_t)nb * N * 3, cudaMemcpyHostToDevice, st));
+        int rc = enqueue_batch(e, d_frames, nb, nullptr, out_best_host ? d_best_img : nullptr, nullptr, nullptr,
+                               d_types, d_light, st);
+        if (rc) return rc;
+        if (out_all_host)
+            CU(cudaMemcpyAsync(out_all_host + (size_t)done * S * N * 3, e->ws + e->L.out, (size_t)nb * S * N * 3, cudaMemcpyDeviceToHost, st));
+        if (out_best_host)
+            CU(cudaMemcpyAsync(out_best_host + (size_t)done * N * 3, d_best_img, (size_t)nb * N * 3, cudaMemcpyDeviceToHost, st));
+        if (scores_host)
+            CU(cudaMemcpyAsync(scores_host + (size_t)done * S * kScoreCols, e->ws + e->L.scores, sizeof(double) * nb * S * kScoreCols, cudaMemcpyDeviceToHost, st));
+        if (best_host) CU(cudaMemcpyAsync(best_host + done, e->ws + e->L.best, sizeof(int) * nb, cudaMemcpyDeviceToHost, st));
+        if (type_host) CU(cudaMemcpyAsync(type_host + done, d_types, sizeof(int) * nb, cudaMemcpyDeviceToHost, st));
+        if (light_host) CU(cudaMemcpyAsync(light_host + (size_t)done * 3, d_light, sizeof(float) * nb * 3, cudaMemcpyDeviceToHost, st));
+    }
+    return uwie_engine_check(e, stream);
+}
+
+const void* uwie_engine_debug(const uwie_engine* e, const char* name, size_t* bytes) {
+    if (!e || !name) return nullptr;
+    const Layout& L = e->L;
+    const size_t B = e->B, S = e->S, N = (size_t)e->H * e->W, nd = e->n_dehaze;
+    const size_t tsz = e->lib.f64 ? 8 : 4;
+    struct Item { const char* n; size_t off, sz; };
+    const Item items[] = {
+        {"frame_hist", L.frame_hist, B * 768 * 4},
+        {"cast", L.cast, B * sizeof(CastTables)},
+        {"tables", L.tables, B * S * sizeof(StratTables)},
+        {"rects", L.rects, B * sizeof(QuadRect)},
+        {"q_trace", L.q_trace, B * kQuadLevelsMax * 4 * 8},
+        {"quad_counts", L.quad_counts, nd ? B * kQuadLevelsMax * 4 * 4 : 0},
+        {"quad_hist", L.quad_hist, nd ? B * kQuadLevelsMax * 4 * 768 * 4 : 0},
+        {"light", L.light, B * 3 * 4},
+        {"ab", L.ab, B * nd * 2 * N * 8},
+        {"recovered", L.recovered, B * nd * N * 3 * tsz},
+        {"tile_lut", L.tile_lut, e->max_tiles ? B * S * kMaxTiles * 256 : 0},
+        {"out_hist", L.out_hist, B * S * 768 * 4},
+        {"out", L.out, B * S * N * 3},
+        {"gray", L.gray, B * S * N},
+        {"qa", L.qa, B * S * sizeof(QaAccum)},
+        {"edge_counts", L.edge_counts, B * S * 4},
+        {"targets", L.targets, B * nd * kSelTargets * sizeof(SelTarget)},
+        {"scores", L.scores, B * S * kScoreCols * 8},
+        {"map", L.map, B * S * N},
+    };
+    for (const Item& it : items) {
+        if (std::strcmp(it.n, name) == 0) {
+            if (bytes) *bytes = it.sz;
+            return e->ws + it.off;
+        }
+    }
+    return nullptr;
+}
+
+}  // extern "C"
