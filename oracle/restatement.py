@@ -419,14 +419,14 @@ def np_percentile_plan(n: int, q, f32: bool):
     """(k, gamma) NumPy's linear method uses for percentile q of n values.
 
     For float32 data NumPy 2.x divides q by float32(100) and evaluates the virtual index
-    n*q + (1 + q*(1-1-1)) - 1 in float32 (numpy/lib/_function_base_impl.py, percentile and
-    _compute_virtual_index); for float64 data everything is float64.  Exposed so host-logic tests
+    (n - 1) * q in float32 (numpy/lib/_function_base_impl.py, percentile and
+    _QuantileMethods['linear']); for float64 data everything is float64.  Exposed so host-logic tests
     can pin the C++ planner against it."""
     if f32:
         qq = np.true_divide(q, np.float32(100))
     else:
         qq = np.true_divide(q, 100)
-    vi = n * qq + (1 + qq * (1 - 1 - 1)) - 1
+    vi = (n - 1) * qq
     k = math.floor(float(vi))
     if float(vi) >= n - 1:
         return n - 1, type(vi)(0)

@@ -77,8 +77,18 @@ template <class T>
 __global__ void __launch_bounds__(768) setup_frame_luts_kernel(SetupArgs a) {
     const int b = blockIdx.x, s = blockIdx.y;
     const Recipe& rc = a.recipes[s];
-    if (rc.dehaze) return;
     const int c = threadIdx.x >> 8, v = threadIdx.x & 255;
+    if (rc.dehaze) {
+        // dehaze -> stretch -> CLAHE -> gamma (SS:231-249): the tail is a table over the CLAHE
+        // output byte; the stretches in front are float-domain and come from k_select.cu
+        if (rc.clahe) {
+            StratTables& sd = a.tables[(size_t)blockIdx.x * a.S + s];
+            const T y = apply_gamma<T>(Ar<T>::div((T)v, (T)255), rc);
+            sd.postf[c][v] = (double)y;
+            sd.postq[c][v] = (uint8_t)quantise<T>(y);
+        }
+        return;
+    }
     __shared__ double val[3][256];
     __shared__ unsigned hq[3][256];
     __shared__ uint8_t eq[3][256];

@@ -49,14 +49,11 @@ void build_color_tables(ColorTables* t) {
 }
 
 // NumPy's 'linear' percentile of n values (numpy/lib/_function_base_impl.py,
-// _compute_virtual_index + _get_gamma): virtual index n*q + (1 + q*(1-1-1)) - 1 with
-// q = pct / 100 evaluated in the data's own float type.
+// _QuantileMethods['linear'] + _get_gamma): virtual index (n - 1) * q with q = pct / 100, both
+// evaluated in the data's own float type (NumPy 2.x divides by a.dtype.type(100)).
 PercentilePlan percentile_plan_f32(long long n, double pct) {
     volatile float q = (float)pct / 100.0f;
-    volatile float nq = (float)n * q;
-    volatile float mid = 1.0f + q * -1.0f;
-    volatile float s = nq + mid;
-    volatile float vi = s - 1.0f;
+    volatile float vi = (float)(n - 1) * q;      // 'linear': (n - 1) * quantiles, in the data's float type
     PercentilePlan p;
     if (vi >= (float)(n - 1)) { p.k = n - 1; p.gamma = 0.0; return p; }
     const float fl = std::floor(vi);
@@ -69,10 +66,7 @@ PercentilePlan percentile_plan_f32(long long n, double pct) {
 
 PercentilePlan percentile_plan_f64(long long n, double pct) {
     volatile double q = pct / 100.0;
-    volatile double nq = (double)n * q;
-    volatile double mid = 1.0 + q * -1.0;
-    volatile double s = nq + mid;
-    volatile double vi = s - 1.0;
+    volatile double vi = (double)(n - 1) * q;
     PercentilePlan p;
     if (vi >= (double)(n - 1)) { p.k = n - 1; p.gamma = 0.0; return p; }
     const double fl = std::floor(vi);
