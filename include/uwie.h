@@ -117,6 +117,16 @@ int uwie_engine_check(uwie_engine* e, void* stream);
 /* Kernels launched by the last uwie_enhance_score call on this engine. */
 int uwie_engine_last_launches(const uwie_engine* e);
 
+/* Per-stage device timing.  uwie_engine_profile(e, 1) clears the record and makes every following
+ * uwie_enhance_score[_host] call bracket each stage of its kernel sequence with CUDA events on the
+ * call's stream; (e, 0) stops.  uwie_engine_profile_read synchronises those events and returns, per
+ * stage name (UWIE_STAGE_NAME_LEN bytes each, NUL-terminated), the summed milliseconds, the number
+ * of kernels launched and the number of times the stage ran.  Returns the number of stages (<= cap)
+ * or a negative uwie_status. */
+#define UWIE_STAGE_NAME_LEN 32
+int uwie_engine_profile(uwie_engine* e, int enable);
+int uwie_engine_profile_read(uwie_engine* e, char* names, double* ms, int* kernels, int* runs, int cap);
+
 /* Test hook: device pointer and byte size of a named intermediate of the last run
  * ("frame_hist", "cast", "tables", "rects", "q_trace", "quad_counts", "light", "ab", "recovered",
  *  "tile_lut", "out_hist", "gray", "qa", "edge_counts", "targets").  NULL if unknown. */

@@ -16,7 +16,9 @@ OK, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_SELECT = 0, -1, -2, -3, -4
 # every symbol include/uwie.h declares (tests check that the library exports all of them)
 EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_bytes", "uwie_engine_create",
            "uwie_engine_destroy", "uwie_enhance_score", "uwie_enhance_score_host", "uwie_engine_check",
-           "uwie_engine_last_launches", "uwie_engine_debug")
+           "uwie_engine_last_launches", "uwie_engine_debug", "uwie_engine_profile",
+           "uwie_engine_profile_read")
+STAGE_NAME_LEN = 32
 
 
 class Strategy(C.Structure):
@@ -73,6 +75,11 @@ def load() -> C.CDLL:
     lib.uwie_engine_last_launches.restype = C.c_int
     lib.uwie_engine_debug.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_size_t)]
     lib.uwie_engine_debug.restype = C.c_void_p
+    lib.uwie_engine_profile.argtypes = [C.c_void_p, C.c_int]
+    lib.uwie_engine_profile.restype = C.c_int
+    lib.uwie_engine_profile_read.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_int),
+                                             C.POINTER(C.c_int), C.c_int]
+    lib.uwie_engine_profile_read.restype = C.c_int
     _lib = lib
     return lib
 

@@ -10,10 +10,10 @@ namespace uwie {
 
 constexpr int kStrategiesMax = 6;
 constexpr int kScoreCols = 9;        // total + 8 sub-scores
-constexpr int kSelBins = 1026;       // first-level bins of the percentile selection
-constexpr int kSelSub = 1024;        // second-level bins
+constexpr int kSelBinsA = 4096;      // first-level bins of the percentile selection (12-bit digit)
+constexpr int kSelSub = 1024;        // second- and third-level bins (10-bit digits)
 constexpr int kSelTargets = 24;      // 3 channels x 2 stretches x (lo, hi) x (k, k+1)
-constexpr int kSelCap = 16384;       // gathered candidates per target
+constexpr int kSelTable = 1024;      // float64 only: distinct values ranked inside a final bin
 constexpr int kQuadLevelsMax = 24;   // log2 of the largest supported side, with slack
 
 // cv2 BORDER_REFLECT_101: -1 -> 1, n -> n-2

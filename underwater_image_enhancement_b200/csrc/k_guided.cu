@@ -120,8 +120,8 @@ __global__ void __launch_bounds__(NT) gf_recover_kernel(GuidedArgs a) {
     double* sA = smem;                 // [span]
     double* sB = sA + span;            // [span]
     double* ring = sB + span;          // [r][NT]
-    unsigned* shist = reinterpret_cast<unsigned*>(ring + (size_t)r * NT);   // [3][kSelBins]
-    for (int i = threadIdx.x; i < 3 * kSelBins; i += NT) shist[i] = 0;
+    unsigned* shist = reinterpret_cast<unsigned*>(ring + (size_t)r * NT);   // [3][kSelBinsA]
+    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += NT) shist[i] = 0;
     const CastTables& ct = a.cast[b];
     const float l0 = a.light[b * 3], l1 = a.light[b * 3 + 1], l2 = a.light[b * 3 + 2];
     const uint8_t* frame = a.frames + (size_t)b * a.H * a.W * 3;
@@ -172,14 +172,14 @@ __global__ void __launch_bounds__(NT) gf_recover_kernel(GuidedArgs a) {
                     const double rec = __dadd_rn(__ddiv_rn((double)__fsub_rn(ct.curf[c][vb], lc), t), (double)lc);
                     const T v = clip01<T>((T)rec);
                     o[c] = v;
-                    atomicAdd(&shist[c * kSelBins + sel_bin_a<T>(v)], 1u);
+                    atomicAdd(&shist[c * kSelBinsA + (sel_prefix<T>(v) >> 20)], 1u);
                 }
             }
         }
         __syncthreads();
     }
-    unsigned* gh = a.sel_hist_a + (size_t)inst * 3 * kSelBins;
-    for (int i = threadIdx.x; i < 3 * kSelBins; i += NT) {
+    unsigned* gh = a.sel_hist_a + (size_t)inst * 3 * kSelBinsA;
+    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += NT) {
         const unsigned v = shist[i];
         if (v) atomicAdd(&gh[i], v);
     }
@@ -198,7 +198,7 @@ int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st) {
     }
     {
         const size_t sm = ((size_t)2 * (128 + max_radius - 1) + (size_t)max_radius * NT) * sizeof(double) +
-                          (size_t)3 * kSelBins * sizeof(unsigned);
+                          (size_t)3 * kSelBinsA * sizeof(unsigned);
         dim3 grid((a.W + 127) / 128, chunks, inst);
         if (a.lib.f64) {
             cudaFuncSetAttribute(gf_recover_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);

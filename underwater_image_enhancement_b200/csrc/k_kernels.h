@@ -90,14 +90,13 @@ struct GuidedArgs {
     const float* light;          // [B][3]
     double* ab;                  // [B * n_dehaze][2][H][W]
     void* recovered;             // [B * n_dehaze][H][W][3] in the library's float type
-    unsigned* sel_hist_a;        // [B * n_dehaze][3][kSelBins]
+    unsigned* sel_hist_a;        // [B * n_dehaze][3][kSelBinsA]
 };
 int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st);
 
 struct SelTarget {
-    long long rank;   // rank still to resolve inside the current bin
-    int bin_a, bin_b;
-    int count;        // gathered candidates
+    long long rank;      // rank still to resolve inside the current bin
+    unsigned prefix;     // digits resolved so far (12, 22, then 32 bits of sel_prefix)
     int active;
 };
 struct SelectArgs {
@@ -108,10 +107,12 @@ struct SelectArgs {
     int n_dehaze;
     int dehaze_idx[kStrategiesMax];
     const void* recovered;
-    const unsigned* sel_hist_a;  // [inst][3][kSelBins]
+    const unsigned* sel_hist_a;  // [inst][3][kSelBinsA]
     unsigned* sel_hist_b;        // [inst][kSelTargets][kSelSub]
+    unsigned* sel_hist_c;        // [inst][kSelTargets][kSelSub]
     SelTarget* targets;          // [inst][kSelTargets]
-    void* sel_buf;               // [inst][kSelTargets][kSelCap] in the library's float type
+    unsigned long long* tab_keys;   // float64 only: [inst][kSelTargets][kSelTable], 0 = empty, else bits + 1
+    unsigned* tab_counts;           //               [inst][kSelTargets][kSelTable]
     StratTables* tables;         // [B][S]
     int* status;
 };

@@ -38,10 +38,11 @@ struct Bump {
 
 struct Layout {
     // zeroed every run (contiguous)
-    size_t zero_begin, frame_hist, quad_hist, quad_counts, sel_hist_a, sel_hist_b, out_hist, qa,
+    size_t zero_begin, frame_hist, quad_hist, quad_counts, sel_hist_a, sel_hist_b, sel_hist_c, tab_keys,
+        tab_counts, out_hist, qa,
         edge_counts, zero_end;
     size_t recipes, ctab, status, types, cast, tables, rects, q_trace, light, map, labels, ab,
-        recovered, targets, sel_buf, tile_lut, out, gray, cf_part, scores, best;
+        recovered, targets, tile_lut, out, gray, cf_part, scores, best;
     size_t total;
 };
 
@@ -62,6 +63,11 @@ struct uwie_engine {
     char* ws = nullptr;
     bool owns_ws = false;
     int last_launches = 0;
+    // per-stage timing (uwie_engine_profile): events[i] opens record i, events[i + 1] closes it
+    bool prof_on = false;
+    struct Mark { const char* name; cudaEvent_t ev; int kernels; };
+    std::vector<Mark> marks;
+    std::vector<cudaEvent_t> ev_pool;
     // pinned staging for the host entry point
     uint8_t* pin_frames = nullptr;
     template <class T> T* at(size_t off) const { return reinterpret_cast<T*>(ws + off); }
@@ -133,8 +139,11 @@ void plan_layout(uwie_engine* e) {
     L.frame_hist = b.take(B * 768 * 4);
     L.quad_hist = b.take(nd ? B * kQuadLevelsMax * 4 * 768 * 4 : 0);
     L.quad_counts = b.take(nd ? B * kQuadLevelsMax * 4 * 4 : 0);
-    L.sel_hist_a = b.take(B * nd * 3 * kSelBins * 4);
+    L.sel_hist_a = b.take(B * nd * 3 * kSelBinsA * 4);
     L.sel_hist_b = b.take(B * nd * kSelTargets * kSelSub * 4);
+    L.sel_hist_c = b.take(B * nd * kSelTargets * kSelSub * 4);
+    L.tab_keys = b.take(e->lib.f64 ? B * nd * kSelTargets * kSelTable * 8 : 0);
+    L.tab_counts = b.take(e->lib.f64 ? B * nd * kSelTargets * kSelTable * 4 : 0);
     L.out_hist = b.take(B * S * 768 * 4);
     L.qa = b.take(B * S * sizeof(QaAccum));
     L.edge_counts = b.take(B * S * 4);
@@ -153,7 +162,6 @@ void plan_layout(uwie_engine* e) {
     L.ab = b.take(B * nd * 2 * N * 8);
     L.recovered = b.take(B * nd * N * 3 * tsz);
     L.targets = b.take(B * nd * kSelTargets * sizeof(SelTarget));
-    L.sel_buf = b.take(B * nd * kSelTargets * kSelCap * tsz);
     L.tile_lut = b.take(e->max_tiles ? B * S * kMaxTiles * 256 : 0);
     L.out = b.take(B * S * N * 3);
     L.gray = b.take(B * S * N);
@@ -292,7 +300,9 @@ int uwie_engine_create(uwie_engine** out, const uwie_library* lib, const uwie_st
 void uwie_engine_destroy(uwie_engine* e) {
     if (!e) return;
     if (e->owns_ws && e->ws) cudaFree(e->ws);
-    if (e->pin_frames) cudaFreeHost(e->pin_frames);
+    if (e->pin_frames) cudaFree(e->pin_frames);
+    for (auto& m : e->marks) cudaEventDestroy(m.ev);
+    for (auto& ev : e->ev_pool) cudaEventDestroy(ev);
     delete e;
 }
 
@@ -324,16 +334,30 @@ __global__ void gather_best_kernel(const uint8_t* __restrict__ all, const int* _
     }
 }
 
+// Stage bracket: closes the previous stage (kernel count = launches since its mark) and opens `name`.
+// name == nullptr only closes.  No-op unless profiling is on.
+void stage(uwie_engine* e, cudaStream_t st, const char* name, int launches_so_far) {
+    if (!e->prof_on) return;
+    if (!e->marks.empty() && e->marks.back().name) e->marks.back().kernels = launches_so_far - e->marks.back().kernels;
+    cudaEvent_t ev;
+    if (!e->ev_pool.empty()) { ev = e->ev_pool.back(); e->ev_pool.pop_back(); }
+    else if (cudaEventCreate(&ev) != cudaSuccess) { e->prof_on = false; return; }
+    cudaEventRecord(ev, st);
+    e->marks.push_back({name, ev, launches_so_far});
+}
+
 int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out_all, uint8_t* out_best,
                   double* scores, int32_t* best, int32_t* types, float* light, cudaStream_t st) {
     const Layout& L = e->L;
     const int S = e->S, H = e->H, W = e->W;
     const size_t N = (size_t)H * W;
     int launches = 0;
+    stage(e, st, "zero", launches);
     CU(cudaMemsetAsync(e->ws + L.zero_begin, 0, L.zero_end - L.zero_begin, st));
 
     uint8_t* out_buf = out_all ? out_all : e->at<uint8_t>(L.out);
 
+    stage(e, st, "frame_hist", launches);
     launches += launch_frame_hist(frames, batch, H, W, e->at<unsigned>(L.frame_hist), st);
 
     SetupArgs sa;
@@ -344,6 +368,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     sa.types = e->at<int>(L.types);
     sa.cast = e->at<CastTables>(L.cast);
     sa.tables = e->at<StratTables>(L.tables);
+    stage(e, st, "setup_luts", launches);
     launches += launch_setup_cast(sa, st);
     launches += launch_setup_frame_luts(sa, st);
 
@@ -355,6 +380,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         qa.counts = e->at<unsigned>(L.quad_counts);
         qa.q_trace = e->at<double>(L.q_trace);
         qa.light = e->at<float>(L.light);
+        stage(e, st, "quadtree_canny", launches);
         launches += launch_quad_init(qa, st);
         CannyArgs ca;
         std::memset(&ca, 0, sizeof(ca));
@@ -379,6 +405,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;
         ga.ab = e->at<double>(L.ab); ga.recovered = e->at<void>(L.recovered);
         ga.sel_hist_a = e->at<unsigned>(L.sel_hist_a);
+        stage(e, st, "guided_recover", launches);
         launches += launch_guided(ga, e->max_radius, st);
 
         SelectArgs se;
@@ -389,9 +416,12 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         se.recovered = ga.recovered; se.sel_hist_a = ga.sel_hist_a;
         se.sel_hist_b = e->at<unsigned>(L.sel_hist_b);
         se.targets = e->at<SelTarget>(L.targets);
-        se.sel_buf = e->at<void>(L.sel_buf);
+        se.sel_hist_c = e->at<unsigned>(L.sel_hist_c);
+        se.tab_keys = e->at<unsigned long long>(L.tab_keys);
+        se.tab_counts = e->at<unsigned>(L.tab_counts);
         se.tables = sa.tables;
         se.status = e->at<int>(L.status);
+        stage(e, st, "percentile_select", launches);
         launches += launch_select(se, st);
     }
 
@@ -407,11 +437,14 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     aa.out = out_buf; aa.gray = e->at<uint8_t>(L.gray);
     aa.qa = e->at<QaAccum>(L.qa); aa.cf_part = e->at<double>(L.cf_part);
     aa.pix_per_block = e->pix_per_block; aa.final_blocks = e->final_blocks;
+    stage(e, st, "clahe_tile_luts", launches);
     launches += launch_clahe_luts(aa, e->max_tiles, st);
     if (e->need_hist_pass) {
+        stage(e, st, "clahe_out_hist", launches);
         launches += launch_apply(aa, false, st);
         launches += launch_setup_post_luts(sa, st);
     }
+    stage(e, st, "final_apply", launches);
     launches += launch_apply(aa, true, st);
 
     CannyArgs cq;
@@ -420,6 +453,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     cq.gray = aa.gray; cq.planes_per_img = S;
     cq.map = e->at<uint8_t>(L.map); cq.labels = e->at<int>(L.labels);
     cq.counts = e->at<unsigned>(L.edge_counts);
+    stage(e, st, "score_canny", launches);
     launches += launch_canny(cq, H, W, batch * S, st);
 
     ScoreArgs sc;
@@ -427,8 +461,10 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     sc.qa = aa.qa; sc.cf_part = aa.cf_part; sc.final_blocks = e->final_blocks;
     sc.edge_counts = e->at<unsigned>(L.edge_counts);
     sc.scores = e->at<double>(L.scores); sc.best = e->at<int>(L.best);
+    stage(e, st, "scores", launches);
     launches += launch_scores(sc, st);
 
+    stage(e, st, "gather_copy", launches);
     if (out_best) {
         gather_best_kernel<<<dim3(64, batch), 256, 0, st>>>(out_buf, sc.best, S, N * 3, out_best);
         ++launches;
@@ -437,6 +473,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     if (best) CU(cudaMemcpyAsync(best, sc.best, sizeof(int) * batch, cudaMemcpyDeviceToDevice, st));
     if (types) CU(cudaMemcpyAsync(types, sa.types, sizeof(int) * batch, cudaMemcpyDeviceToDevice, st));
     if (light) CU(cudaMemcpyAsync(light, e->at<float>(L.light), sizeof(float) * batch * 3, cudaMemcpyDeviceToDevice, st));
+    stage(e, st, nullptr, launches);
     CU(cudaGetLastError());
     e->last_launches = launches;
     return UWIE_OK;
@@ -505,6 +542,37 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
         if (light_host) CU(cudaMemcpyAsync(light_host + (size_t)done * 3, d_light, sizeof(float) * nb * 3, cudaMemcpyDeviceToHost, st));
     }
     return uwie_engine_check(e, stream);
+}
+
+int uwie_engine_profile(uwie_engine* e, int enable) {
+    if (!e) return fail(UWIE_ERR_ARG, "null engine");
+    for (auto& m : e->marks) e->ev_pool.push_back(m.ev);
+    e->marks.clear();
+    e->prof_on = enable != 0;
+    return UWIE_OK;
+}
+
+int uwie_engine_profile_read(uwie_engine* e, char* names, double* ms, int* kernels, int* runs, int cap) {
+    if (!e || !names || !ms || !kernels || !runs || cap < 1) return fail(UWIE_ERR_ARG, "bad profile_read arguments");
+    int n = 0;
+    for (size_t i = 0; i + 1 < e->marks.size(); ++i) {
+        const auto& m = e->marks[i];
+        if (!m.name) continue;                       // closing mark of a call
+        CU(cudaEventSynchronize(e->marks[i + 1].ev));
+        float t = 0.f;
+        CU(cudaEventElapsedTime(&t, m.ev, e->marks[i + 1].ev));
+        int k = 0;
+        while (k < n && std::strncmp(names + (size_t)k * UWIE_STAGE_NAME_LEN, m.name, UWIE_STAGE_NAME_LEN - 1) != 0) ++k;
+        if (k == n) {
+            if (n == cap) continue;
+            std::memset(names + (size_t)k * UWIE_STAGE_NAME_LEN, 0, UWIE_STAGE_NAME_LEN);
+            std::strncpy(names + (size_t)k * UWIE_STAGE_NAME_LEN, m.name, UWIE_STAGE_NAME_LEN - 1);
+            ms[k] = 0.0; kernels[k] = 0; runs[k] = 0;
+            ++n;
+        }
+        ms[k] += t; kernels[k] += m.kernels; runs[k] += 1;
+    }
+    return n;
 }
 
 const void* uwie_engine_debug(const uwie_engine* e, const char* name, size_t* bytes) {

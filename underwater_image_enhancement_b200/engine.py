@@ -70,7 +70,8 @@ class Engine:
             pass
 
     # ------------------------------------------------------------------ device path
-    def run(self, frames: torch.Tensor, want_all=True, want_best=False, out_all=None, out_best=None):
+    def run(self, frames: torch.Tensor, want_all=True, want_best=False, out_all=None, out_best=None,
+            scores=None, best=None, types=None, light=None):
         """frames: uint8 CUDA tensor [B, H, W, 3], B <= max_batch.  Asynchronous on the current stream."""
         if frames.dtype != torch.uint8 or frames.dim() != 4 or frames.shape[1:] != (self.H, self.W, 3):
             raise ValueError(f"frames must be uint8 [B,{self.H},{self.W},3], got {tuple(frames.shape)} {frames.dtype}")
@@ -83,10 +84,17 @@ class Engine:
             out_all = torch.empty((B, self.S, self.H, self.W, 3), dtype=torch.uint8, device=dev)
         if want_best and out_best is None:
             out_best = torch.empty((B, self.H, self.W, 3), dtype=torch.uint8, device=dev)
-        scores = torch.empty((B, self.S, _lib.SCORE_COLS), dtype=torch.float64, device=dev)
-        best = torch.empty((B,), dtype=torch.int32, device=dev)
-        types = torch.empty((B,), dtype=torch.int32, device=dev)
-        light = torch.empty((B, 3), dtype=torch.float32, device=dev)
+        for t in (out_all, out_best, scores, best, types, light):
+            if t is not None and not (t.is_cuda and t.is_contiguous()):
+                raise ValueError("output tensors must be contiguous CUDA tensors")
+        if scores is None:
+            scores = torch.empty((B, self.S, _lib.SCORE_COLS), dtype=torch.float64, device=dev)
+        if best is None:
+            best = torch.empty((B,), dtype=torch.int32, device=dev)
+        if types is None:
+            types = torch.empty((B,), dtype=torch.int32, device=dev)
+        if light is None:
+            light = torch.empty((B, 3), dtype=torch.float32, device=dev)
         stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         with torch.cuda.device(dev):
             _lib.check(self._lib.uwie_enhance_score(self._h, _ptr(frames), B, _ptr(out_all), _ptr(out_best),
@@ -130,6 +138,27 @@ class Engine:
                                                          hp(scores), hp(best), hp(types), hp(light), stream))
         return {"out": out_all, "best_out": out_best, "scores": scores, "best": best, "type": types,
                 "light": light}
+
+    # ------------------------------------------------------------------ per-stage device timing
+    def profile(self, enable: bool = True):
+        _lib.check(self._lib.uwie_engine_profile(self._h, 1 if enable else 0))
+
+    def profile_read(self):
+        """[(stage, ms_total, kernels_launched, runs)] since profile(True); synchronises."""
+        cap = 64
+        names = C.create_string_buffer(cap * _lib.STAGE_NAME_LEN)
+        ms = (C.c_double * cap)()
+        ker = (C.c_int * cap)()
+        runs = (C.c_int * cap)()
+        with torch.cuda.device(self.device):
+            n = self._lib.uwie_engine_profile_read(self._h, names, ms, ker, runs, cap)
+        if n < 0:
+            _lib.check(n)
+        out = []
+        for i in range(n):
+            raw = names.raw[i * _lib.STAGE_NAME_LEN:(i + 1) * _lib.STAGE_NAME_LEN]
+            out.append((raw.split(b"\0", 1)[0].decode(), float(ms[i]), int(ker[i]), int(runs[i])))
+        return out
 
     # ------------------------------------------------------------------ test hook
     def debug(self, name: str, dtype, shape=None) -> np.ndarray:
