@@ -203,7 +203,7 @@ def run_native(args):
     import torch
     import torch.distributed as dist
 
-    from underwater_image_enhancement_b200 import _lib
+    from underwater_image_enhancement_b200 import _lib, shard
     from underwater_image_enhancement_b200.engine import Engine
     from underwater_image_enhancement_b200.synth import synth_image
 
@@ -228,7 +228,6 @@ def run_native(args):
     scores = torch.empty((B, S, 9), dtype=torch.float64, device=dev)
     best = torch.empty((B,), dtype=torch.int32, device=dev)
     types = torch.empty((B,), dtype=torch.int32, device=dev)
-    gathered = torch.empty((world * B, S * 9 + 2), dtype=torch.float64, device=dev) if world > 1 else None
     eng = Engine(args.library, H, W, max_batch=chunk, device=str(dev))
 
     launches = [0]
@@ -240,8 +239,7 @@ def run_native(args):
                     best=best[c0:c1], types=types[c0:c1])
             launches[0] += eng.last_launches
         if world > 1:      # the path's only exchange: per-image score records to every rank (rank 0 reads them)
-            rec = torch.cat([scores.view(B, -1), best.double()[:, None], types.double()[:, None]], dim=1)
-            dist.all_gather_into_tensor(gathered, rec)
+            shard.gather_records(shard.pack_records(scores, best, types, B))
 
     def barrier():
         if world > 1:
