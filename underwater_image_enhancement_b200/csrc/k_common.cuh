@@ -10,10 +10,11 @@ namespace uwie {
 
 constexpr int kStrategiesMax = 6;
 constexpr int kScoreCols = 9;        // total + 8 sub-scores
-constexpr int kSelBinsA = 4096;      // first-level bins of the percentile selection (12-bit digit)
-constexpr int kSelSub = 1024;        // second- and third-level bins (10-bit digits)
+constexpr int kSelBinsA = 1056;      // first-level bins of the percentile selection: key >> 21 in [0, 1024], padded to 33 * 32
+constexpr int kSelBinsB = 2048;      // second level: 11 bits
+constexpr int kSelBinsC = 1024;      // third level: 10 bits
 constexpr int kSelTargets = 24;      // 3 channels x 2 stretches x (lo, hi) x (k, k+1)
-constexpr int kSelTable = 1024;      // float64 only: distinct values ranked inside a final bin
+constexpr int kSelTable = 256;       // distinct values ranked inside a final bin of width 2^-31 (hash table slots)
 constexpr int kQuadLevelsMax = 24;   // log2 of the largest supported side, with slack
 
 // cv2 BORDER_REFLECT_101: -1 -> 1, n -> n-2

@@ -1,14 +1,22 @@
-// Dehaze core in float64: dark-channel transmission, guided filter, scene recovery.
+// Dehaze core: dark-channel transmission, guided filter, scene recovery.
 //   estimate_transmission / guided_filter / restore_image   six_stadigy.py:25-46, 167-188
 //   estimate_transmission / guided_filter / recover_image   enhancement_strategies.py:16-46, 209-249
 // Box means are cv2.boxFilter(CV_64F, (r, r)): normalised, anchor r//2 (window [-(r//2), r-1-r//2]),
 // BORDER_REFLECT_101, scale applied as a multiplication by 1/(r*r).
 //
-// Two marching kernels.  A block owns a strip of columns and walks down a chunk of rows, keeping the
-// last r rows of horizontal window sums in a shared-memory ring and the vertical sums in registers:
-//   gf_ab_kernel       frame bytes -> I (gray/255), p (raw transmission) -> a, b   (4 box sums)
-//   gf_recover_kernel  a, b -> mean_a * I + mean_b -> t -> (img - A)/t + A -> recovered frame
-//                      (+ the first, coarse level of the percentile histograms, see k_select.cu)
+// Three kernels:
+//   gf_prep_kernel      frame bytes -> gray plane (uint8) and dark-channel plane (float32), per frame
+//   gf_ab_kernel        gray, dark -> box sums of I, p, I*p, I*I -> a, b (float64 planes)
+//   gf_recover_kernel   a, b -> mean_a * I + mean_b -> t -> (img - A)/t + A -> recovered frame
+//                       (+ the first level of the percentile histograms, see k_select.cu)
+//
+// Box sums are O(1) per pixel.  Every WARP marches down its own strip of 160 columns with no
+// block-level synchronisation: a lane keeps the vertical running sums of 5 columns in registers
+// (row entering the window added, row leaving it subtracted - both re-read, so there is no ring
+// buffer), publishes them to a per-warp shared-memory row, and then forms the horizontal window
+// sums of 5 CONSECUTIVE outputs with a sliding window (r + 4 reads for 5 outputs).
+// The first-pass sums are exact whatever the order: I = g/255 is carried as the integers (sum g,
+// sum g*g), and p (a float32, multiple of 2^-27) and g*p are summed in float64 far below 2^53 ulps.
 #include "k_arith.cuh"
 #include "k_kernels.h"
 
@@ -16,170 +24,270 @@ namespace uwie {
 
 namespace {
 
-constexpr int NT = 256;
+constexpr int GC = 5;                 // columns per lane (odd: conflict-free 64-bit shared accesses)
+constexpr int GSPAN = 32 * GC;        // columns a warp carries, outputs = GSPAN - r + 1
+constexpr int GWARPS = 8;
+constexpr int GNT = 32 * GWARPS;
 
-__device__ __forceinline__ float raw_transmission(const CastTables& ct, const float* lg, float omega,
-                                                  int clip_t0, int r, int g, int b) {
-    // dark = min_c(img / (A + guard)); t0 = 1 - omega * dark, all float32
-    float d = __fdiv_rn(ct.curf[0][r], lg[0]);
-    d = fminf(d, __fdiv_rn(ct.curf[1][g], lg[1]));
-    d = fminf(d, __fdiv_rn(ct.curf[2][b], lg[2]));
-    float t0 = __fsub_rn(1.0f, __fmul_rn(omega, d));
-    if (clip_t0) t0 = t0 < 0.1f ? 0.1f : (t0 > 1.0f ? 1.0f : t0);
+// ------------------------------------------------------------------ gray + dark channel planes
+__global__ void __launch_bounds__(256) gf_prep_kernel(GuidedArgs a) {
+    const int b = blockIdx.y;
+    __shared__ float sdiv[3][256];      // img / (A + guard), float32            SS:170, ES:221
+    __shared__ uint8_t sq[3][256];      // byte cv2 sees for the (colour-corrected) frame
+    const CastTables& ct = a.cast[b];
+    for (int i = threadIdx.x; i < 768; i += 256) {
+        const int c = i >> 8, v = i & 255;
+        const float lg = __fadd_rn(a.light[b * 3 + c], (float)a.lib.dark_guard);
+        sdiv[c][v] = __fdiv_rn(ct.curf[c][v], lg);
+        sq[c][v] = ct.curq[c][v];
+    }
+    __syncthreads();
+    const size_t npix = (size_t)a.H * a.W;
+    const uint8_t* f = a.frames + (size_t)b * npix * 3;
+    uint8_t* gp = a.gray_plane + (size_t)b * npix;
+    float* dp = a.dark_plane + (size_t)b * npix;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < npix; i += (size_t)gridDim.x * 256) {
+        const int r = f[i * 3], g = f[i * 3 + 1], bl = f[i * 3 + 2];
+        gp[i] = (uint8_t)gray_q15(sq[0][r], sq[1][g], sq[2][bl]);
+        dp[i] = fminf(fminf(sdiv[0][r], sdiv[1][g]), sdiv[2][bl]);
+    }
+}
+
+__device__ __forceinline__ float transmission0(float omega, int clip_t0, float dark) {
+    float t0 = __fsub_rn(1.0f, __fmul_rn(omega, dark));           // 1 - omega * dark, float32
+    if (clip_t0) t0 = t0 < 0.1f ? 0.1f : (t0 > 1.0f ? 1.0f : t0); // SS:174
     return t0;
 }
 
+struct Strip {
+    int r, lo, hi, outw, xs, ys, ye, warp, lane;
+    bool valid;
+};
+__device__ __forceinline__ Strip make_strip(const GuidedArgs& a, int r) {
+    Strip s;
+    s.r = r; s.lo = r / 2; s.hi = r - 1 - s.lo;
+    s.outw = GSPAN - r + 1;
+    s.warp = threadIdx.x >> 5; s.lane = threadIdx.x & 31;
+    s.xs = (blockIdx.x * GWARPS + s.warp) * s.outw;
+    s.ys = blockIdx.y * a.rows_per_block;
+    s.ye = min(s.ys + a.rows_per_block, a.H);
+    s.valid = s.xs < a.W && s.ys < s.ye;
+    return s;
+}
+
 // ------------------------------------------------------------------ a, b
-// thread <-> (column = tid / 4, quantity = tid % 4) with quantities I, p, I*p, I*I ; TW = 64
-__global__ void __launch_bounds__(NT) gf_ab_kernel(GuidedArgs a) {
-    constexpr int TW = 64;
-    extern __shared__ double smem[];
-    const int inst = blockIdx.z;                      // frame * n_dehaze + k
+__global__ void __launch_bounds__(GNT) gf_ab_kernel(GuidedArgs a) {
+    __shared__ double sP[GWARPS][GSPAN];
+    __shared__ double sGP[GWARPS][GSPAN];
+    __shared__ unsigned long long sG[GWARPS][GSPAN];     // (sum g) << 32 | sum g*g
+    const int inst = blockIdx.z;                         // frame * n_dehaze + k
     const int b = inst / a.n_dehaze, k = inst % a.n_dehaze;
     const Recipe& rc = a.recipes[a.dehaze_idx[k]];
-    const int r = rc.radius, lo = r / 2, hi = r - 1 - lo;
-    const int x0 = blockIdx.x * TW;
-    const int ys = blockIdx.y * a.rows_per_block;
-    const int ye = min(ys + a.rows_per_block, a.H);
-    if (ys >= ye) return;
-    const int span = TW + r - 1;
-    double* sI = smem;                 // [span]
-    double* sP = sI + span;            // [span]
-    double* ring = sP + span;          // [r][NT]
-    __shared__ float lg[3];
-    const CastTables& ct = a.cast[b];
-    if (threadIdx.x < 3)
-        lg[threadIdx.x] = __fadd_rn(a.light[b * 3 + threadIdx.x], (float)a.lib.dark_guard);
-    __syncthreads();
-    const uint8_t* frame = a.frames + (size_t)b * a.H * a.W * 3;
-    const int col = threadIdx.x >> 2, q = threadIdx.x & 3;
-    const int x = x0 + col;
-    const double scale = 1.0 / ((double)r * (double)r);
-    double* pa = a.ab + (size_t)inst * 2 * a.H * a.W;
-    double* pb = pa + (size_t)a.H * a.W;
+    const Strip s = make_strip(a, rc.radius);
+    if (!s.valid) return;                                // warp-uniform
+    const float omega = rc.omega;
+    const int clip_t0 = a.lib.clip_t0;
+    const double eps = rc.eps;
+    const size_t npix = (size_t)a.H * a.W;
+    const uint8_t* gray = a.gray_plane + (size_t)b * npix;
+    const float* dark = a.dark_plane + (size_t)b * npix;
+    double* pa = a.ab + (size_t)inst * 2 * npix;
+    double* pb = pa + npix;
+    const double rr = (double)s.r * (double)s.r;
+    const double scale = 1.0 / rr;                       // cv2: sum * (1 / (kw * kh))
+    const double scale_i = 1.0 / (255.0 * rr), scale_ii = 1.0 / (65025.0 * rr);
+    double* wP = sP[s.warp]; double* wGP = sGP[s.warp]; unsigned long long* wG = sG[s.warp];
 
-    double vsum = 0.0;
-    int filled = 0, slot = 0;
-    for (int yy = ys - lo; yy < ye + hi; ++yy) {
-        const int y = reflect101(yy, a.H);
-        for (int i = threadIdx.x; i < span; i += NT) {
-            const int xx = reflect101(x0 - lo + i, a.W);
-            const uint8_t* p = frame + ((size_t)y * a.W + xx) * 3;
-            const int r0 = p[0], g0 = p[1], b0 = p[2];
-            const int gr = gray_q15(ct.curq[0][r0], ct.curq[1][g0], ct.curq[2][b0]);
-            sI[i] = (double)gr / 255.0;
-            sP[i] = (double)raw_transmission(ct, lg, rc.omega, a.lib.clip_t0, r0, g0, b0);
+    int cx[GC];
+#pragma unroll
+    for (int j = 0; j < GC; ++j) cx[j] = reflect101(s.xs - s.lo + s.lane + 32 * j, a.W);
+    double vp[GC], vgp[GC];
+    unsigned long long vg[GC];
+#pragma unroll
+    for (int j = 0; j < GC; ++j) { vp[j] = 0.0; vgp[j] = 0.0; vg[j] = 0ull; }
+
+    auto row_add = [&](int yy) {
+        const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+#pragma unroll
+        for (int j = 0; j < GC; ++j) {
+            const unsigned g = gray[ro + cx[j]];
+            const double p = (double)transmission0(omega, clip_t0, dark[ro + cx[j]]);
+            vp[j] += p; vgp[j] += (double)g * p;
+            vg[j] += ((unsigned long long)g << 32) | (unsigned long long)(g * g);
         }
-        __syncthreads();
-        double h = 0.0;
-        if (q == 0) { for (int i = 0; i < r; ++i) h += sI[col + i]; }
-        else if (q == 1) { for (int i = 0; i < r; ++i) h += sP[col + i]; }
-        else if (q == 2) { for (int i = 0; i < r; ++i) h += __dmul_rn(sI[col + i], sP[col + i]); }
-        else { for (int i = 0; i < r; ++i) h += __dmul_rn(sI[col + i], sI[col + i]); }
-        vsum += h;
-        if (filled >= r) vsum -= ring[slot * NT + threadIdx.x];
-        ring[slot * NT + threadIdx.x] = h;
-        slot = slot + 1 == r ? 0 : slot + 1;
-        ++filled;
-        if (filled >= r) {
-            const int yo = yy - hi;                  // output row of the window that just filled
-            const double m = vsum * scale;
-            const int base = (threadIdx.x & 31) & ~3;
-            const double mI = __shfl_sync(0xffffffffu, m, base);
-            const double mP = __shfl_sync(0xffffffffu, m, base + 1);
-            const double mIP = __shfl_sync(0xffffffffu, m, base + 2);
-            const double mII = __shfl_sync(0xffffffffu, m, base + 3);
-            const double cov = __dsub_rn(mIP, __dmul_rn(mI, mP));
-            const double var = __dsub_rn(mII, __dmul_rn(mI, mI));
-            const double av = __ddiv_rn(cov, __dadd_rn(var, rc.eps));
-            const double bv = __dsub_rn(mP, __dmul_rn(av, mI));
-            if (x < a.W) {
-                if (q == 0) pa[(size_t)yo * a.W + x] = av;
-                else if (q == 1) pb[(size_t)yo * a.W + x] = bv;
+    };
+    auto row_sub = [&](int yy) {
+        const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+#pragma unroll
+        for (int j = 0; j < GC; ++j) {
+            const unsigned g = gray[ro + cx[j]];
+            const double p = (double)transmission0(omega, clip_t0, dark[ro + cx[j]]);
+            vp[j] -= p; vgp[j] -= (double)g * p;
+            vg[j] -= ((unsigned long long)g << 32) | (unsigned long long)(g * g);
+        }
+    };
+
+    for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) row_add(yy);
+    const int base = s.lane * GC;
+    for (int yo = s.ys; yo < s.ye; ++yo) {
+        row_add(yo + s.hi);
+#pragma unroll
+        for (int j = 0; j < GC; ++j) {
+            wP[s.lane + 32 * j] = vp[j]; wGP[s.lane + 32 * j] = vgp[j]; wG[s.lane + 32 * j] = vg[j];
+        }
+        __syncwarp();
+        double ra[GC], rb[GC];
+        if (base < s.outw) {
+            double hp = 0.0, hgp = 0.0;
+            unsigned long long hg = 0ull;
+            for (int i = 0; i < s.r; ++i) { hp += wP[base + i]; hgp += wGP[base + i]; hg += wG[base + i]; }
+#pragma unroll
+            for (int j = 0; j < GC; ++j) {
+                if (j > 0 && base + j < s.outw) {
+                    hp += wP[base + j + s.r - 1] - wP[base + j - 1];
+                    hgp += wGP[base + j + s.r - 1] - wGP[base + j - 1];
+                    hg += wG[base + j + s.r - 1] - wG[base + j - 1];
+                }
+                const double mI = (double)(unsigned)(hg >> 32) * scale_i;
+                const double mII = (double)(unsigned)(hg & 0xffffffffull) * scale_ii;
+                const double mP = hp * scale;
+                const double mIP = hgp * scale_i;
+                const double cov = __dsub_rn(mIP, __dmul_rn(mI, mP));
+                const double var = __dsub_rn(mII, __dmul_rn(mI, mI));
+                ra[j] = __ddiv_rn(cov, __dadd_rn(var, eps));
+                rb[j] = __dsub_rn(mP, __dmul_rn(ra[j], mI));
             }
         }
-        __syncthreads();
+        __syncwarp();
+        if (base < s.outw) {
+#pragma unroll
+            for (int j = 0; j < GC; ++j) { wP[base + j] = ra[j]; wGP[base + j] = rb[j]; }
+        }
+        __syncwarp();
+        const size_t ro = (size_t)yo * a.W;
+        for (int i = s.lane; i < s.outw; i += 32) {
+            const int x = s.xs + i;
+            if (x < a.W) { pa[ro + x] = wP[i]; pb[ro + x] = wGP[i]; }
+        }
+        __syncwarp();
+        row_sub(yo - s.lo);
     }
 }
 
 // ------------------------------------------------------------------ recover
-// thread <-> (column = tid / 2, quantity = tid % 2) with quantities a, b ; TW = 128
 template <class T>
-__global__ void __launch_bounds__(NT) gf_recover_kernel(GuidedArgs a) {
-    constexpr int TW = 128;
-    extern __shared__ double smem[];
+__global__ void __launch_bounds__(GNT) gf_recover_kernel(GuidedArgs a) {
+    __shared__ double sA[GWARPS][GSPAN];
+    __shared__ double sB[GWARPS][GSPAN];
+    __shared__ double sI[256];                 // g / 255.0
+    __shared__ float sdiff[3][256];            // img - A, float32              SS:185, ES:247
+    __shared__ unsigned shist[3 * kSelBinsA];
     const int inst = blockIdx.z;
     const int b = inst / a.n_dehaze, k = inst % a.n_dehaze;
     const Recipe& rc = a.recipes[a.dehaze_idx[k]];
-    const int r = rc.radius, lo = r / 2, hi = r - 1 - lo;
-    const int x0 = blockIdx.x * TW;
-    const int ys = blockIdx.y * a.rows_per_block;
-    const int ye = min(ys + a.rows_per_block, a.H);
-    if (ys >= ye) return;
-    const int span = TW + r - 1;
-    double* sA = smem;                 // [span]
-    double* sB = sA + span;            // [span]
-    double* ring = sB + span;          // [r][NT]
-    unsigned* shist = reinterpret_cast<unsigned*>(ring + (size_t)r * NT);   // [3][kSelBinsA]
-    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += NT) shist[i] = 0;
-    const CastTables& ct = a.cast[b];
     const float l0 = a.light[b * 3], l1 = a.light[b * 3 + 1], l2 = a.light[b * 3 + 2];
-    const uint8_t* frame = a.frames + (size_t)b * a.H * a.W * 3;
-    const int col = threadIdx.x >> 1, q = threadIdx.x & 1;
-    const int x = x0 + col;
-    const double scale = 1.0 / ((double)r * (double)r);
-    const double* pa = a.ab + (size_t)inst * 2 * a.H * a.W;
-    const double* pb = pa + (size_t)a.H * a.W;
-    T* out = reinterpret_cast<T*>(a.recovered) + (size_t)inst * a.H * a.W * 3;
-    __syncthreads();
-
-    double vsum = 0.0;
-    int filled = 0, slot = 0;
-    for (int yy = ys - lo; yy < ye + hi; ++yy) {
-        const int y = reflect101(yy, a.H);
-        for (int i = threadIdx.x; i < span; i += NT) {
-            const int xx = reflect101(x0 - lo + i, a.W);
-            sA[i] = pa[(size_t)y * a.W + xx];
-            sB[i] = pb[(size_t)y * a.W + xx];
+    {
+        const CastTables& ct = a.cast[b];
+        for (int i = threadIdx.x; i < 3 * kSelBinsA; i += GNT) shist[i] = 0;
+        for (int i = threadIdx.x; i < 256; i += GNT) sI[i] = (double)i / 255.0;
+        for (int i = threadIdx.x; i < 768; i += GNT) {
+            const int c = i >> 8, v = i & 255;
+            sdiff[c][v] = __fsub_rn(ct.curf[c][v], c == 0 ? l0 : (c == 1 ? l1 : l2));
         }
-        __syncthreads();
-        double h = 0.0;
-        const double* src = q == 0 ? sA : sB;
-        for (int i = 0; i < r; ++i) h += src[col + i];
-        vsum += h;
-        if (filled >= r) vsum -= ring[slot * NT + threadIdx.x];
-        ring[slot * NT + threadIdx.x] = h;
-        slot = slot + 1 == r ? 0 : slot + 1;
-        ++filled;
-        if (filled >= r) {
-            const int yo = yy - hi;
-            const double m = vsum * scale;
-            const int base = (threadIdx.x & 31) & ~1;
-            const double mA = __shfl_sync(0xffffffffu, m, base);
-            const double mB = __shfl_sync(0xffffffffu, m, base + 1);
-            if (x < a.W) {
-                const uint8_t* p = frame + ((size_t)yo * a.W + x) * 3;
-                const int r0 = p[0], g0 = p[1], b0 = p[2];
-                const int gr = gray_q15(ct.curq[0][r0], ct.curq[1][g0], ct.curq[2][b0]);
-                double t = __dadd_rn(__dmul_rn(mA, (double)gr / 255.0), mB);
-                t = t < 0.1 ? 0.1 : (t > 1.0 ? 1.0 : t);
-                T* o = out + ((size_t)yo * a.W + x) * 3;
-                // (img - A) in float32, / t and + A in float64, stored in the library's float type
-                const int c_lo = q == 0 ? 0 : 2, c_hi = q == 0 ? 2 : 3;
-                for (int c = c_lo; c < c_hi; ++c) {
-                    const int vb = c == 0 ? r0 : (c == 1 ? g0 : b0);
-                    const float lc = c == 0 ? l0 : (c == 1 ? l1 : l2);
-                    const double rec = __dadd_rn(__ddiv_rn((double)__fsub_rn(ct.curf[c][vb], lc), t), (double)lc);
-                    const T v = clip01<T>((T)rec);
-                    o[c] = v;
-                    atomicAdd(&shist[c * kSelBinsA + (sel_prefix<T>(v) >> 20)], 1u);
+    }
+    __syncthreads();
+    const Strip s = make_strip(a, rc.radius);
+    if (s.valid) {
+        const size_t npix = (size_t)a.H * a.W;
+        const uint8_t* frame = a.frames + (size_t)b * npix * 3;
+        const uint8_t* gray = a.gray_plane + (size_t)b * npix;
+        const double* pa = a.ab + (size_t)inst * 2 * npix;
+        const double* pb = pa + npix;
+        T* out = reinterpret_cast<T*>(a.recovered) + (size_t)inst * npix * 3;
+        const double scale = 1.0 / ((double)s.r * (double)s.r);
+        double* wA = sA[s.warp]; double* wB = sB[s.warp];
+        const double dl0 = (double)l0, dl1 = (double)l1, dl2 = (double)l2;
+
+        int cx[GC];
+#pragma unroll
+        for (int j = 0; j < GC; ++j) cx[j] = reflect101(s.xs - s.lo + s.lane + 32 * j, a.W);
+        double va[GC], vb[GC];
+#pragma unroll
+        for (int j = 0; j < GC; ++j) { va[j] = 0.0; vb[j] = 0.0; }
+        auto row_add = [&](int yy) {
+            const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+#pragma unroll
+            for (int j = 0; j < GC; ++j) { va[j] += pa[ro + cx[j]]; vb[j] += pb[ro + cx[j]]; }
+        };
+        auto row_sub = [&](int yy) {
+            const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+#pragma unroll
+            for (int j = 0; j < GC; ++j) { va[j] -= pa[ro + cx[j]]; vb[j] -= pb[ro + cx[j]]; }
+        };
+        for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) row_add(yy);
+        const int base = s.lane * GC;
+        for (int yo = s.ys; yo < s.ye; ++yo) {
+            row_add(yo + s.hi);
+#pragma unroll
+            for (int j = 0; j < GC; ++j) { wA[s.lane + 32 * j] = va[j]; wB[s.lane + 32 * j] = vb[j]; }
+            __syncwarp();
+            double ma[GC], mb[GC];
+            if (base < s.outw) {
+                double ha = 0.0, hb = 0.0;
+                for (int i = 0; i < s.r; ++i) { ha += wA[base + i]; hb += wB[base + i]; }
+#pragma unroll
+                for (int j = 0; j < GC; ++j) {
+                    if (j > 0 && base + j < s.outw) {
+                        ha += wA[base + j + s.r - 1] - wA[base + j - 1];
+                        hb += wB[base + j + s.r - 1] - wB[base + j - 1];
+                    }
+                    ma[j] = ha * scale; mb[j] = hb * scale;
                 }
             }
+            __syncwarp();
+            if (base < s.outw) {
+#pragma unroll
+                for (int j = 0; j < GC; ++j) { wA[base + j] = ma[j]; wB[base + j] = mb[j]; }
+            }
+            __syncwarp();
+            const size_t ro = (size_t)yo * a.W;
+            for (int i = s.lane; i < s.outw; i += 32) {
+                const int x = s.xs + i;
+                if (x >= a.W) break;
+                const uint8_t* p = frame + (ro + x) * 3;
+                const int r0 = p[0], g0 = p[1], b0 = p[2];
+                double t = __dadd_rn(__dmul_rn(wA[i], sI[gray[ro + x]]), wB[i]);
+                t = t < 0.1 ? 0.1 : (t > 1.0 ? 1.0 : t);
+                // (img - A) in float32, / t and + A in float64, stored in the library's float type
+                double q0, q1, q2;
+                if (sizeof(T) == 8) {
+                    q0 = __ddiv_rn((double)sdiff[0][r0], t);
+                    q1 = __ddiv_rn((double)sdiff[1][g0], t);
+                    q2 = __ddiv_rn((double)sdiff[2][b0], t);
+                } else {
+                    // float32 buffers: x * (1/t) differs from x / t by at most 1 ulp of float64, which
+                    // survives the rounding to float32 with probability ~1e-8 per value
+                    const double it = __drcp_rn(t);
+                    q0 = __dmul_rn((double)sdiff[0][r0], it);
+                    q1 = __dmul_rn((double)sdiff[1][g0], it);
+                    q2 = __dmul_rn((double)sdiff[2][b0], it);
+                }
+                const T v0 = clip01<T>((T)__dadd_rn(q0, dl0));
+                const T v1 = clip01<T>((T)__dadd_rn(q1, dl1));
+                const T v2 = clip01<T>((T)__dadd_rn(q2, dl2));
+                T* o = out + (ro + x) * 3;
+                o[0] = v0; o[1] = v1; o[2] = v2;
+                atomicAdd(&shist[0 * kSelBinsA + (sel_key<T>(v0) >> 21)], 1u);
+                atomicAdd(&shist[1 * kSelBinsA + (sel_key<T>(v1) >> 21)], 1u);
+                atomicAdd(&shist[2 * kSelBinsA + (sel_key<T>(v2) >> 21)], 1u);
+            }
+            __syncwarp();
+            row_sub(yo - s.lo);
         }
-        __syncthreads();
     }
+    __syncthreads();
     unsigned* gh = a.sel_hist_a + (size_t)inst * 3 * kSelBinsA;
-    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += NT) {
+    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += GNT) {
         const unsigned v = shist[i];
         if (v) atomicAdd(&gh[i], v);
     }
@@ -190,25 +298,20 @@ __global__ void __launch_bounds__(NT) gf_recover_kernel(GuidedArgs a) {
 int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st) {
     if (a.n_dehaze == 0) return 0;
     const int inst = a.B * a.n_dehaze;
+    const size_t npix = (size_t)a.H * a.W;
+    int pb = (int)((npix + 256 * 8 - 1) / (256 * 8));
+    if (pb > 148 * 8) pb = 148 * 8;
+    gf_prep_kernel<<<dim3(pb, a.B), 256, 0, st>>>(a);
     const int chunks = (a.H + a.rows_per_block - 1) / a.rows_per_block;
-    {
-        const size_t sm = ((size_t)2 * (64 + max_radius - 1) + (size_t)max_radius * NT) * sizeof(double);
-        cudaFuncSetAttribute(gf_ab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        gf_ab_kernel<<<dim3((a.W + 63) / 64, chunks, inst), NT, sm, st>>>(a);
-    }
-    {
-        const size_t sm = ((size_t)2 * (128 + max_radius - 1) + (size_t)max_radius * NT) * sizeof(double) +
-                          (size_t)3 * kSelBinsA * sizeof(unsigned);
-        dim3 grid((a.W + 127) / 128, chunks, inst);
-        if (a.lib.f64) {
-            cudaFuncSetAttribute(gf_recover_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-            gf_recover_kernel<double><<<grid, NT, sm, st>>>(a);
-        } else {
-            cudaFuncSetAttribute(gf_recover_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-            gf_recover_kernel<float><<<grid, NT, sm, st>>>(a);
-        }
-    }
-    return 2;
+    // strips are sized by each instance's own radius; the grid covers the largest radius present
+    // (fewest outputs per strip); for a smaller radius the surplus warps exit at once
+    const int outw_min = GSPAN - max_radius + 1;
+    const int strips = (a.W + outw_min - 1) / outw_min;
+    dim3 grid((strips + GWARPS - 1) / GWARPS, chunks, inst);
+    gf_ab_kernel<<<grid, GNT, 0, st>>>(a);
+    if (a.lib.f64) gf_recover_kernel<double><<<grid, GNT, 0, st>>>(a);
+    else gf_recover_kernel<float><<<grid, GNT, 0, st>>>(a);
+    return 3;
 }
 
 }  // namespace uwie

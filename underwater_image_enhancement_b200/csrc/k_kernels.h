@@ -85,6 +85,8 @@ struct GuidedArgs {
     int n_dehaze;                // number of dehaze strategies
     int dehaze_idx[kStrategiesMax];   // their strategy indices
     int rows_per_block;
+    uint8_t* gray_plane;         // [B][H][W]   gray byte of the (colour-corrected) frame
+    float* dark_plane;           // [B][H][W]   min_c img / (A + guard)
     const uint8_t* frames;
     const CastTables* cast;
     const float* light;          // [B][3]
@@ -96,8 +98,10 @@ int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st);
 
 struct SelTarget {
     long long rank;      // rank still to resolve inside the current bin
-    unsigned prefix;     // digits resolved so far (12, 22, then 32 bits of sel_prefix)
+    unsigned prefix;     // digits of the key resolved so far (11, 22, then all 32 bits)
     int active;
+    int rep;             // target of the same channel whose histogram / table this one shares
+    int pad;
 };
 struct SelectArgs {
     int B, S;
@@ -108,11 +112,11 @@ struct SelectArgs {
     int dehaze_idx[kStrategiesMax];
     const void* recovered;
     const unsigned* sel_hist_a;  // [inst][3][kSelBinsA]
-    unsigned* sel_hist_b;        // [inst][kSelTargets][kSelSub]
-    unsigned* sel_hist_c;        // [inst][kSelTargets][kSelSub]
+    unsigned* sel_hist_b;        // [inst][kSelTargets][kSelBinsB]
+    unsigned* sel_hist_c;        // [inst][kSelTargets][kSelBinsC]
     SelTarget* targets;          // [inst][kSelTargets]
-    unsigned long long* tab_keys;   // float64 only: [inst][kSelTargets][kSelTable], 0 = empty, else bits + 1
-    unsigned* tab_counts;           //               [inst][kSelTargets][kSelTable]
+    unsigned long long* tab_keys;   // [inst][kSelTargets][kSelTable], 0 = empty, else bit pattern + 1
+    unsigned* tab_counts;           // [inst][kSelTargets][kSelTable]
     StratTables* tables;         // [B][S]
     int* status;
 };

@@ -1,16 +1,20 @@
 // Exact np.percentile on float data (the recovered frame of the dehaze strategies):
 //   enhance_contrast / white_balance   six_stadigy.py:190-199, 210-219   (float32 data)
 //   color_enhancement                  enhancement_strategies.py:252-273 (float64 data)
-// np.percentile(method='linear') needs the order statistics k and k+1.  They are found exactly by
-// a most-significant-digit radix selection over the IEEE bit pattern (monotone for values in [0,1]):
-// a 32-bit prefix p of every value is cut into digits of 12 / 10 / 10 bits,
-//   float32: p = the bit pattern itself            -> three levels resolve the value completely
-//   float64: p = bit pattern >> 30 (exponent + 22 mantissa bits); the members of the final bin
-//            (normally 1-3 distinct values, or one value repeated many times) are put into a small
-//            hash table of (full bit pattern, count) and ranked there.
-// Level A is histogrammed inside gf_recover_kernel; levels B and C cost one read of the data each.
+// np.percentile(method='linear') needs the order statistics k and k+1.  They are found exactly by a
+// most-significant-digit radix selection over key = floor(x * 2^31) (k_arith.cuh: monotone, uniform
+// in value, exact), cut into digits of 11 / 11 / 10 bits:
+//   level A  histogram of key >> 21, accumulated inside gf_recover_kernel (no extra pass)
+//   level B  one streaming read: members of each target's A bin, by their next 11 bits
+//   level C  one streaming read: members of each target's A.B bin, by their last 10 bits
+// After level C a float32 value >= 2^-8 is known exactly (key * 2^-31).  Values that can share a
+// key (float64 data; float32 below 2^-8) are told apart by a small hash table of (bit pattern, count)
+// filled in one more streaming read that exits at once when no target needs it.
 // Heavy ties are the normal case, not a corner case: every pixel whose channel byte equals the
-// airlight's byte recovers to exactly A_c, whatever its transmission.
+// airlight's byte recovers to exactly A_c, whatever its transmission - hence counts, not lists.
+// Because a level-A bin is 1/1024 of the value range, few elements match a target after level A;
+// the streaming passes therefore test one shared-memory byte per element (does my A bin hold any
+// target of my channel?) and only the rare hits do warp-aggregated global atomics.
 // A second stretch applied on top of the first is a monotone map of already ranked data, so its
 // order statistics are the mapped order statistics of the recovered frame: no further pass.
 #include "k_arith.cuh"
@@ -21,6 +25,7 @@ namespace uwie {
 namespace {
 
 constexpr int NT = 256;
+constexpr unsigned kExactKeyMin = 1u << 23;     // float32: key >= 2^23  <=>  x >= 2^-8  <=>  key is injective
 
 __device__ __forceinline__ long long target_rank(const Recipe& rc, long long n, int t) {
     // t = stretch * 4 + endpoint * 2 + j
@@ -32,7 +37,6 @@ __device__ __forceinline__ long long target_rank(const Recipe& rc, long long n, 
 }
 
 // ---- scans: one warp per target walks the histogram of the current level
-// LEVEL 0: level-A histogram [inst][3][kSelBinsA]; 1: sel_hist_b; 2: sel_hist_c
 template <int LEVEL>
 __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a) {
     const int inst = blockIdx.x, tg = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -41,17 +45,18 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
     if (LEVEL == 0) {
         const Recipe& rc = a.recipes[a.dehaze_idx[inst % a.n_dehaze]];
         rank = target_rank(rc, a.n, tg & 7);
-        if (lane == 0) { T.active = rank >= 0; T.prefix = 0; T.rank = rank; }
-        if (rank < 0) return;
+        if (lane == 0) { T.active = rank >= 0; T.prefix = 0; T.rank = rank; T.rep = tg; }
     } else {
-        if (!T.active) return;
-        rank = T.rank;
+        rank = T.active ? T.rank : -1;
     }
     __syncwarp();
-    const int nbins = LEVEL == 0 ? kSelBinsA : kSelSub;
+    if (rank >= 0) {
+    constexpr int nbins = LEVEL == 0 ? kSelBinsA : (LEVEL == 1 ? kSelBinsB : kSelBinsC);
+    constexpr int bits = LEVEL == 1 ? 11 : 10;
     const unsigned* h = LEVEL == 0 ? a.sel_hist_a + ((size_t)inst * 3 + (tg >> 3)) * kSelBinsA
-                                   : (LEVEL == 1 ? a.sel_hist_b : a.sel_hist_c) + ((size_t)inst * kSelTargets + tg) * kSelSub;
-    const int per = nbins / 32;
+                      : LEVEL == 1 ? a.sel_hist_b + ((size_t)inst * kSelTargets + T.rep) * kSelBinsB
+                                   : a.sel_hist_c + ((size_t)inst * kSelTargets + T.rep) * kSelBinsC;
+    constexpr int per = nbins / 32;
     long long mine = 0;
     for (int i = 0; i < per; ++i) mine += h[lane * per + i];
     long long incl = mine;
@@ -65,7 +70,6 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
     const unsigned who = __ballot_sync(0xffffffffu, here);
     if (who == 0) {             // cannot happen (ranks are < n); keep the run alive and flag it
         if (lane == 0) { atomicOr(a.status, UWIE_STATUS_SELECT_INTERNAL); T.active = 0; }
-        return;
     }
     if (here) {
         long long acc = excl;
@@ -76,51 +80,99 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
             acc = nx;
         }
         T.rank = rank - acc;
-        T.prefix = LEVEL == 0 ? (unsigned)bin : ((T.prefix << 10) | (unsigned)bin);
+        T.prefix = LEVEL == 0 ? (unsigned)bin : ((T.prefix << bits) | (unsigned)bin);
+    }
+    }
+    // targets of one channel that sit in the same bin share one histogram at the next level:
+    // rep = the first such target (k and k+1 of a percentile almost always coincide)
+    __syncthreads();
+    if (lane == 0) {
+        int rep = tg;
+        if (T.active) {
+            for (int o = (tg & ~7); o < tg; ++o) {
+                const SelTarget& O = a.targets[(size_t)inst * kSelTargets + o];
+                if (O.active && O.prefix == T.prefix) { rep = o; break; }
+            }
+        }
+        T.rep = rep;
     }
 }
 
-// ---- level B / C histograms: members of each target's current bin, by their next 10 bits
-template <class T, int LEVEL>
-__global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
-    extern __shared__ unsigned sh[];          // [kSelTargets][kSelSub]
-    const int inst = blockIdx.y;
-    __shared__ unsigned s_pre[kSelTargets];
-    __shared__ int s_on[kSelTargets];
-    for (int i = threadIdx.x; i < kSelTargets * kSelSub; i += NT) sh[i] = 0;
+// Shared prologue of the streaming passes: the targets of this instance and, per channel, which
+// level-A bins hold a target at all.
+struct PassState {
+    unsigned pre[kSelTargets];
+    int on[kSelTargets];
+    uint8_t hot[3][kSelBinsA];
+};
+template <int LEVEL>      // 1, 2: prefixes hold 11 / 22 bits; 3: all 32
+__device__ __forceinline__ bool pass_prologue(const SelectArgs& a, int inst, PassState& ps, bool only_inexact) {
+    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += NT) (&ps.hot[0][0])[i] = 0;
+    __syncthreads();
     if (threadIdx.x < kSelTargets) {
         const SelTarget& t = a.targets[(size_t)inst * kSelTargets + threadIdx.x];
-        // a target that shares its bin with the previous one of its channel rides on that histogram
-        s_pre[threadIdx.x] = t.prefix;
-        s_on[threadIdx.x] = t.active;
+        int on = t.active;
+        if (only_inexact && t.prefix >= kExactKeyMin) on = 0;     // float32 value already exact
+        if (t.rep != (int)threadIdx.x) on = 0;                     // rides on its representative's histogram
+        ps.pre[threadIdx.x] = t.prefix;
+        ps.on[threadIdx.x] = on;
+        if (on) ps.hot[threadIdx.x >> 3][LEVEL == 1 ? t.prefix : (LEVEL == 2 ? t.prefix >> 11 : t.prefix >> 21)] = 1;
     }
-    __syncthreads();
-    constexpr int SHIFT = LEVEL == 1 ? 20 : 10;
+    return __syncthreads_or(threadIdx.x < kSelTargets && ps.on[threadIdx.x]) != 0;
+}
+
+// warp-aggregated histogram increment for the lanes in `hits` (all of them call this)
+__device__ __forceinline__ void agg_add(unsigned* h, unsigned bin, unsigned hits) {
+    const unsigned same = __match_any_sync(hits, bin);
+    if ((int)(__ffs(same) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&h[bin], (unsigned)__popc(same));
+}
+
+// ---- level B / C: one streaming read of the recovered frame of an instance
+template <class T, int LEVEL>
+__global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
+    __shared__ PassState ps;
+    const int inst = blockIdx.y;
+    if (!pass_prologue<LEVEL>(a, inst, ps, false)) return;
+    constexpr int SHIFT = LEVEL == 1 ? 21 : 10;                 // key >> SHIFT is what the targets resolved so far
+    constexpr unsigned SUBMASK = LEVEL == 1 ? 2047u : 1023u;
+    constexpr int SUBSHIFT = LEVEL == 1 ? 10 : 0;
+    constexpr int BINS = LEVEL == 1 ? kSelBinsB : kSelBinsC;
     const T* src = reinterpret_cast<const T*>(a.recovered) + (size_t)inst * a.n * 3;
-    const long long total = a.n * 3;
-    for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < total; i += (long long)gridDim.x * NT) {
-        const unsigned p = sel_prefix<T>(src[i]);
-        const int c = (int)(i % 3);
-        const unsigned hi = p >> SHIFT, sub = (p >> (SHIFT - 10)) & 1023u;
+    unsigned* gh = (LEVEL == 1 ? a.sel_hist_b : a.sel_hist_c) + (size_t)inst * kSelTargets * BINS;
+    const long long stride = (long long)gridDim.x * NT;
+    const long long rounds = (a.n + stride - 1) / stride;       // whole warps stay in the loop
+    for (long long rd = 0; rd < rounds; ++rd) {
+        const long long px = rd * stride + (long long)blockIdx.x * NT + threadIdx.x;
+        const bool in = px < a.n;
+        unsigned key[3];
+        bool hot = false;
 #pragma unroll
-        for (int t = 0; t < 8; ++t) {
-            const int tg = c * 8 + t;
-            if (s_on[tg] && s_pre[tg] == hi) atomicAdd(&sh[tg * kSelSub + sub], 1u);
+        for (int c = 0; c < 3; ++c) {
+            key[c] = in ? sel_key<T>(src[px * 3 + c]) : 0u;
+            hot |= in && ps.hot[c][key[c] >> 21];
         }
-    }
-    __syncthreads();
-    unsigned* gh = (LEVEL == 1 ? a.sel_hist_b : a.sel_hist_c) + (size_t)inst * kSelTargets * kSelSub;
-    for (int i = threadIdx.x; i < kSelTargets * kSelSub; i += NT) {
-        const unsigned v = sh[i];
-        if (v) atomicAdd(&gh[i], v);
+        if (__ballot_sync(0xffffffffu, hot) == 0) continue;     // the common case
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const bool hc = in && ps.hot[c][key[c] >> 21];
+            if (__ballot_sync(0xffffffffu, hc) == 0) continue;
+            const unsigned hi = key[c] >> SHIFT, sub = (key[c] >> SUBSHIFT) & SUBMASK;
+            for (int t = 0; t < 8; ++t) {
+                const int tg = c * 8 + t;
+                if (!ps.on[tg]) continue;                        // uniform
+                const bool hit = hc && ps.pre[tg] == hi;
+                const unsigned hits = __ballot_sync(0xffffffffu, hit);
+                if (hit) agg_add(gh + (size_t)tg * BINS, sub, hits);
+            }
+        }
     }
 }
 
-// ---- float64 only: (bit pattern, count) table of the members of each target's final bin
-__device__ __forceinline__ void table_insert(unsigned long long* keys, unsigned* counts, unsigned long long key,
+// ---- values that share a key: (bit pattern, count) table of the members of each target's final bin
+__device__ __forceinline__ void table_insert(unsigned long long* keys, unsigned* counts, unsigned long long bits,
                                              unsigned n, int* status) {
-    const unsigned long long stored = key + 1;          // 0 marks an empty slot
-    unsigned h = (unsigned)((key * 0x9E3779B97F4A7C15ull) >> 54);   // 10 bits
+    const unsigned long long stored = bits + 1;          // 0 marks an empty slot
+    unsigned h = (unsigned)((bits * 0x9E3779B97F4A7C15ull) >> 56) & (kSelTable - 1);
     for (int probe = 0; probe < kSelTable; ++probe) {
         const unsigned long long prev = atomicCAS(&keys[h], 0ull, stored);
         if (prev == 0ull || prev == stored) { atomicAdd(&counts[h], n); return; }
@@ -129,43 +181,45 @@ __device__ __forceinline__ void table_insert(unsigned long long* keys, unsigned*
     atomicOr(status, UWIE_STATUS_SELECT_OVERFLOW);
 }
 
+template <class T>
 __global__ void __launch_bounds__(NT) sel_table_kernel(SelectArgs a) {
+    __shared__ PassState ps;
     const int inst = blockIdx.y;
-    __shared__ unsigned s_pre[kSelTargets];
-    __shared__ int s_on[kSelTargets];
-    if (threadIdx.x < kSelTargets) {
-        const SelTarget& t = a.targets[(size_t)inst * kSelTargets + threadIdx.x];
-        s_pre[threadIdx.x] = t.prefix;
-        s_on[threadIdx.x] = t.active;
-    }
-    __syncthreads();
-    const double* src = reinterpret_cast<const double*>(a.recovered) + (size_t)inst * a.n * 3;
+    if (!pass_prologue<3>(a, inst, ps, sizeof(T) == 4)) return;  // float32: normally nothing to do
+    const T* src = reinterpret_cast<const T*>(a.recovered) + (size_t)inst * a.n * 3;
     unsigned long long* keys = a.tab_keys + (size_t)inst * kSelTargets * kSelTable;
     unsigned* counts = a.tab_counts + (size_t)inst * kSelTargets * kSelTable;
-    const long long total = a.n * 3;
     const long long stride = (long long)gridDim.x * NT;
-    const long long rounds = (total + stride - 1) / stride;
-    for (long long rd = 0; rd < rounds; ++rd) {          // whole warps stay in the loop (match_any below)
-        const long long i = rd * stride + (long long)blockIdx.x * NT + threadIdx.x;
-        const bool in = i < total;
-        const double x = in ? src[i] : 0.0;
-        const unsigned p = sel_prefix<double>(x);
-        const unsigned long long key = sel_key64(x);
-        const int c = (int)(i % 3);
+    const long long rounds = (a.n + stride - 1) / stride;
+    for (long long rd = 0; rd < rounds; ++rd) {
+        const long long px = rd * stride + (long long)blockIdx.x * NT + threadIdx.x;
+        const bool in = px < a.n;
+        T x[3];
+        unsigned key[3];
+        bool hot = false;
 #pragma unroll
-        for (int t = 0; t < 8; ++t) {
-            const int tg = c * 8 + t;
-            const bool hit = in && s_on[tg] && s_pre[tg] == p;
-            const unsigned hits = __ballot_sync(0xffffffffu, hit);
-            if (hits == 0) continue;
-            if (hit) {
-                // lanes of one warp hold consecutive elements: same t means same slot only if same channel,
-                // so aggregate on (target, key)
-                const unsigned long long tag = key ^ ((unsigned long long)tg << 58);
-                const unsigned same = __match_any_sync(hits, tag);
-                if ((int)(__ffs(same) - 1) == (int)(threadIdx.x & 31))
-                    table_insert(keys + (size_t)tg * kSelTable, counts + (size_t)tg * kSelTable, key,
-                                 (unsigned)__popc(same), a.status);
+        for (int c = 0; c < 3; ++c) {
+            x[c] = in ? src[px * 3 + c] : (T)0;
+            key[c] = sel_key<T>(x[c]);
+            hot |= in && ps.hot[c][key[c] >> 21];
+        }
+        if (__ballot_sync(0xffffffffu, hot) == 0) continue;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const bool hc = in && ps.hot[c][key[c] >> 21];
+            if (__ballot_sync(0xffffffffu, hc) == 0) continue;
+            const unsigned long long bits = sel_bits<T>(x[c]);
+            for (int t = 0; t < 8; ++t) {
+                const int tg = c * 8 + t;
+                if (!ps.on[tg]) continue;
+                const bool hit = hc && ps.pre[tg] == key[c];
+                const unsigned hits = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const unsigned same = __match_any_sync(hits, bits);
+                    if ((int)(__ffs(same) - 1) == (int)(threadIdx.x & 31))
+                        table_insert(keys + (size_t)tg * kSelTable, counts + (size_t)tg * kSelTable, bits,
+                                     (unsigned)__popc(same), a.status);
+                }
             }
         }
     }
@@ -179,32 +233,33 @@ __global__ void __launch_bounds__(NT) sel_finish_kernel(SelectArgs a) {
     const int s = a.dehaze_idx[k];
     const Recipe& rc = a.recipes[s];
     __shared__ double s_val[kSelTargets];
-    __shared__ unsigned long long l_key[kSelTable];
+    __shared__ unsigned long long l_bits[kSelTable];
     __shared__ unsigned l_cnt[kSelTable];
     __shared__ int l_n;
     for (int tg = 0; tg < kSelTargets; ++tg) {
         const SelTarget t = a.targets[(size_t)inst * kSelTargets + tg];
         if (!t.active) continue;                       // uniform per block
-        if (sizeof(T) == 4) {
-            if (threadIdx.x == 0) s_val[tg] = (double)__uint_as_float(t.prefix);
+        if (sizeof(T) == 4 && t.prefix >= kExactKeyMin) {
+            // key = x * 2^31 exactly, with at most 24 significant bits
+            if (threadIdx.x == 0) s_val[tg] = (double)__fmul_rn(__uint2float_rn(t.prefix), 4.656612873077393e-10f);
             continue;
         }
         if (threadIdx.x == 0) l_n = 0;
         __syncthreads();
-        const unsigned long long* keys = a.tab_keys + ((size_t)inst * kSelTargets + tg) * kSelTable;
-        const unsigned* counts = a.tab_counts + ((size_t)inst * kSelTargets + tg) * kSelTable;
+        const unsigned long long* keys = a.tab_keys + ((size_t)inst * kSelTargets + t.rep) * kSelTable;
+        const unsigned* counts = a.tab_counts + ((size_t)inst * kSelTargets + t.rep) * kSelTable;
         for (int i = threadIdx.x; i < kSelTable; i += NT) {
             const unsigned long long kv = keys[i];
-            if (kv) { const int pos = atomicAdd(&l_n, 1); l_key[pos] = kv - 1; l_cnt[pos] = counts[i]; }
+            if (kv) { const int pos = atomicAdd(&l_n, 1); l_bits[pos] = kv - 1; l_cnt[pos] = counts[i]; }
         }
         __syncthreads();
         const int m = l_n;
         bool found = false;
         for (int i = threadIdx.x; i < m; i += NT) {
             long long less = 0;
-            for (int j = 0; j < m; ++j) if (l_key[j] < l_key[i]) less += l_cnt[j];
+            for (int j = 0; j < m; ++j) if (l_bits[j] < l_bits[i]) less += l_cnt[j];
             if (less <= t.rank && t.rank < less + (long long)l_cnt[i]) {
-                s_val[tg] = __longlong_as_double((long long)l_key[i]);
+                s_val[tg] = (double)sel_from_bits<T>(l_bits[i]);
                 found = true;
             }
         }
@@ -238,20 +293,13 @@ __global__ void __launch_bounds__(NT) sel_finish_kernel(SelectArgs a) {
 
 template <class T>
 int launch_select_t(const SelectArgs& a, int inst, int nblk, cudaStream_t st) {
-    const size_t sm = (size_t)kSelTargets * kSelSub * sizeof(unsigned);
-    static bool attr_done = false;     // per template instance
-    if (!attr_done) {
-        cudaFuncSetAttribute(sel_hist_kernel<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        cudaFuncSetAttribute(sel_hist_kernel<T, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-        attr_done = true;
-    }
     int launches = 0;
     sel_scan_kernel<0><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
-    sel_hist_kernel<T, 1><<<dim3(nblk, inst), NT, sm, st>>>(a); ++launches;
+    sel_hist_kernel<T, 1><<<dim3(nblk, inst), NT, 0, st>>>(a); ++launches;
     sel_scan_kernel<1><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
-    sel_hist_kernel<T, 2><<<dim3(nblk, inst), NT, sm, st>>>(a); ++launches;
+    sel_hist_kernel<T, 2><<<dim3(nblk, inst), NT, 0, st>>>(a); ++launches;
     sel_scan_kernel<2><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
-    if (sizeof(T) == 8) { sel_table_kernel<<<dim3(nblk, inst), NT, 0, st>>>(a); ++launches; }
+    sel_table_kernel<T><<<dim3(nblk, inst), NT, 0, st>>>(a); ++launches;
     sel_finish_kernel<T><<<inst, NT, 0, st>>>(a); ++launches;
     return launches;
 }
@@ -261,8 +309,11 @@ int launch_select_t(const SelectArgs& a, int inst, int nblk, cudaStream_t st) {
 int launch_select(const SelectArgs& a, cudaStream_t st) {
     if (a.n_dehaze == 0) return 0;
     const int inst = a.B * a.n_dehaze;
-    long long per = (a.n * 3 + NT * 16 - 1) / (NT * 16);
-    int nblk = (int)(per < 1 ? 1 : (per > 296 ? 296 : per));
+    // enough blocks to fill the machine across all instances, few enough that the per-block prologue
+    // (3 KB of flags) stays negligible
+    long long per = (a.n + NT * 8 - 1) / (NT * 8);
+    const int cap = (148 * 8 + inst - 1) / inst < 4 ? 4 : (148 * 8 + inst - 1) / inst;
+    const int nblk = (int)(per < 1 ? 1 : (per > cap ? cap : per));
     return a.lib.f64 ? launch_select_t<double>(a, inst, nblk, st) : launch_select_t<float>(a, inst, nblk, st);
 }
 

@@ -42,7 +42,7 @@ struct Layout {
         tab_counts, out_hist, qa,
         edge_counts, zero_end;
     size_t recipes, ctab, status, types, cast, tables, rects, q_trace, light, map, labels, ab,
-        recovered, targets, tile_lut, out, gray, cf_part, scores, best;
+        recovered, targets, gf_gray, gf_dark, tile_lut, out, gray, cf_part, scores, best;
     size_t total;
 };
 
@@ -140,10 +140,10 @@ void plan_layout(uwie_engine* e) {
     L.quad_hist = b.take(nd ? B * kQuadLevelsMax * 4 * 768 * 4 : 0);
     L.quad_counts = b.take(nd ? B * kQuadLevelsMax * 4 * 4 : 0);
     L.sel_hist_a = b.take(B * nd * 3 * kSelBinsA * 4);
-    L.sel_hist_b = b.take(B * nd * kSelTargets * kSelSub * 4);
-    L.sel_hist_c = b.take(B * nd * kSelTargets * kSelSub * 4);
-    L.tab_keys = b.take(e->lib.f64 ? B * nd * kSelTargets * kSelTable * 8 : 0);
-    L.tab_counts = b.take(e->lib.f64 ? B * nd * kSelTargets * kSelTable * 4 : 0);
+    L.sel_hist_b = b.take(B * nd * kSelTargets * kSelBinsB * 4);
+    L.sel_hist_c = b.take(B * nd * kSelTargets * kSelBinsC * 4);
+    L.tab_keys = b.take(B * nd * kSelTargets * kSelTable * 8);
+    L.tab_counts = b.take(B * nd * kSelTargets * kSelTable * 4);
     L.out_hist = b.take(B * S * 768 * 4);
     L.qa = b.take(B * S * sizeof(QaAccum));
     L.edge_counts = b.take(B * S * 4);
@@ -162,6 +162,8 @@ void plan_layout(uwie_engine* e) {
     L.ab = b.take(B * nd * 2 * N * 8);
     L.recovered = b.take(B * nd * N * 3 * tsz);
     L.targets = b.take(B * nd * kSelTargets * sizeof(SelTarget));
+    L.gf_gray = b.take(nd ? B * N : 0);
+    L.gf_dark = b.take(nd ? B * N * 4 : 0);
     L.tile_lut = b.take(e->max_tiles ? B * S * kMaxTiles * 256 : 0);
     L.out = b.take(B * S * N * 3);
     L.gray = b.take(B * S * N);
@@ -402,6 +404,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         ga.n_dehaze = e->n_dehaze;
         for (int i = 0; i < kStrategiesMax; ++i) ga.dehaze_idx[i] = e->dehaze_idx[i];
         ga.rows_per_block = H >= 512 ? (H + 7) / 8 : (H >= 128 ? (H + 1) / 2 : H);
+        ga.gray_plane = e->at<uint8_t>(L.gf_gray); ga.dark_plane = e->at<float>(L.gf_dark);
         ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;
         ga.ab = e->at<double>(L.ab); ga.recovered = e->at<void>(L.recovered);
         ga.sel_hist_a = e->at<unsigned>(L.sel_hist_a);
