@@ -5,9 +5,17 @@
 // enhancement_strategies.py:180-182 / six_stadigy.py:149-151 (each quadtree block, with the
 // block's own borders).
 //
-// Hysteresis is a fixed number of launches (no host round trip): candidates are linked with a
-// lock-free union-find over a per-plane label array (label = smallest pixel index of the
-// component), every strong pixel flags its root, and candidates whose root is flagged are counted.
+// Hysteresis is a fixed number of launches (no host round trip) built on union-find:
+//   1. canny_tile_kernel   gradient, NMS and classification of a 32x64 tile in shared memory, then
+//                          the tile's candidates are linked by a union-find that lives entirely in
+//                          shared memory.  Written out: class byte, label = pixel index of the
+//                          tile-local root, and on root pixels whether the component holds a
+//                          strong pixel.
+//   2. canny_merge_kernel  only pixels on tile borders link across tiles (lock-free atomicMin
+//                          union-find on the global label plane; trees are at most one deep
+//                          below each tile-local root).
+//   3. canny_flag_kernel   tile-local roots that hold a strong pixel flag their global root.
+//   4. canny_count_kernel  candidates whose global root is flagged are counted.
 #include "k_common.cuh"
 #include "k_kernels.h"
 
@@ -15,10 +23,12 @@ namespace uwie {
 
 namespace {
 
-constexpr int TS = 32;            // output tile side
-constexpr int NT = 256;           // threads per block (32 x 8)
+constexpr int TH = 32, TW = 64;   // tile
+constexpr int NT = 256;
 constexpr int LABEL_FLAG = 0x40000000;
 constexpr int LABEL_MASK = 0x3fffffff;
+// class byte: bit 0 candidate, bit 1 strong pixel, bit 2 tile-local root of a component with a strong pixel
+constexpr int CLS_CAND = 1, CLS_STRONG = 2, CLS_ROOT_STRONG = 4;
 
 struct Job {
     int y0, y1, x0, x1;   // rectangle inside the plane, empty when y0 >= y1
@@ -44,33 +54,37 @@ __device__ __forceinline__ Job make_job(const CannyArgs& a, int inst) {
     return j;
 }
 
-__device__ __forceinline__ int uf_find(volatile int* L, int x) {
+// ---- union-find on a label array (global or shared); label = smallest index of the component
+template <class P>
+__device__ __forceinline__ int uf_find(P L, int x) {
     int l;
     while ((l = (L[x] & LABEL_MASK)) != x) x = l;
     return x;
 }
-
 __device__ __forceinline__ void uf_union(int* L, int a, int b) {
     bool done;
     do {
-        a = uf_find(L, a);
-        b = uf_find(L, b);
+        a = uf_find((volatile int*)L, a);
+        b = uf_find((volatile int*)L, b);
         if (a < b) { const int old = atomicMin(&L[b], a); done = (old == b); b = old; }
         else if (b < a) { const int old = atomicMin(&L[a], b); done = (old == a); a = old; }
         else done = true;
     } while (!done);
 }
 
-// ---- pass 1: gradient, NMS, classification; optional per-channel histogram of the source bytes
+// ---- pass 1
 template <int MODE>
-__global__ void __launch_bounds__(NT) canny_nms_kernel(CannyArgs a) {
+__global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     const Job j = make_job(a, blockIdx.z);
     const int rows = j.y1 - j.y0, cols = j.x1 - j.x0;
-    const int ty0 = blockIdx.y * TS, tx0 = blockIdx.x * TS;
+    const int ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
     if (ty0 >= rows || tx0 >= cols) return;
 
-    __shared__ uint8_t sg[TS + 4][TS + 4];
-    __shared__ uint16_t sm[TS + 2][TS + 2];
+    __shared__ uint8_t sg[TH + 4][TW + 4];
+    __shared__ uint16_t sm[TH + 2][TW + 2];
+    __shared__ uint8_t scls[TH * TW];
+    __shared__ int slab[TH * TW];
+    __shared__ int sstrong[TH * TW / 32];          // bit per tile pixel: root of a component with a strong pixel
     __shared__ unsigned shist[MODE == CANNY_QUADRANTS ? 768 : 1];
 
     const int tid = threadIdx.x;
@@ -82,14 +96,15 @@ __global__ void __launch_bounds__(NT) canny_nms_kernel(CannyArgs a) {
         frame = a.frames + (size_t)j.img * npix * 3;
         ct = a.cast + j.img;
         for (int i = tid; i < 768; i += NT) shist[i] = 0;
-        __syncthreads();
     } else {
         gplane = a.gray + (size_t)j.plane * npix;
     }
+    for (int i = tid; i < TH * TW / 32; i += NT) sstrong[i] = 0;
+    __syncthreads();
 
     // gray with a 2-pixel replicated halo (replication at the RECTANGLE's border)
-    for (int i = tid; i < (TS + 4) * (TS + 4); i += NT) {
-        const int ly = i / (TS + 4), lx = i - ly * (TS + 4);
+    for (int i = tid; i < (TH + 4) * (TW + 4); i += NT) {
+        const int ly = i / (TW + 4), lx = i - ly * (TW + 4);
         const int ry = ty0 + ly - 2, rx = tx0 + lx - 2;
         const int y = j.y0 + clamp_idx(ry, rows), x = j.x0 + clamp_idx(rx, cols);
         int g;
@@ -97,7 +112,7 @@ __global__ void __launch_bounds__(NT) canny_nms_kernel(CannyArgs a) {
             const uint8_t* p = frame + ((size_t)y * a.W + x) * 3;
             const int r0 = p[0], g0 = p[1], b0 = p[2];
             g = gray_q15(ct->curq[0][r0], ct->curq[1][g0], ct->curq[2][b0]);
-            const bool inner = ly >= 2 && ly < TS + 2 && lx >= 2 && lx < TS + 2 && ry < rows && rx < cols;
+            const bool inner = ly >= 2 && ly < TH + 2 && lx >= 2 && lx < TW + 2 && ry < rows && rx < cols;
             if (inner) {
                 atomicAdd(&shist[r0], 1u);
                 atomicAdd(&shist[256 + g0], 1u);
@@ -111,8 +126,8 @@ __global__ void __launch_bounds__(NT) canny_nms_kernel(CannyArgs a) {
     __syncthreads();
 
     // L1 magnitude on the tile + 1 halo; zero outside the rectangle
-    for (int i = tid; i < (TS + 2) * (TS + 2); i += NT) {
-        const int ly = i / (TS + 2), lx = i - ly * (TS + 2);
+    for (int i = tid; i < (TH + 2) * (TW + 2); i += NT) {
+        const int ly = i / (TW + 2), lx = i - ly * (TW + 2);
         const int ry = ty0 + ly - 1, rx = tx0 + lx - 1;
         int m = 0;
         if (ry >= 0 && ry < rows && rx >= 0 && rx < cols) {
@@ -127,29 +142,68 @@ __global__ void __launch_bounds__(NT) canny_nms_kernel(CannyArgs a) {
     }
     __syncthreads();
 
+    // classification; every candidate starts as its own component
+    for (int i = tid; i < TH * TW; i += NT) {
+        const int ly = i / TW, lx = i - ly * TW;
+        const int ry = ty0 + ly, rx = tx0 + lx;
+        int cls = 0;
+        if (ry < rows && rx < cols) {
+            const int cy = ly + 2, cx = lx + 2;
+            const int dx = (sg[cy - 1][cx + 1] + 2 * sg[cy][cx + 1] + sg[cy + 1][cx + 1]) -
+                           (sg[cy - 1][cx - 1] + 2 * sg[cy][cx - 1] + sg[cy + 1][cx - 1]);
+            const int dy = (sg[cy + 1][cx - 1] + 2 * sg[cy + 1][cx] + sg[cy + 1][cx + 1]) -
+                           (sg[cy - 1][cx - 1] + 2 * sg[cy - 1][cx] + sg[cy - 1][cx + 1]);
+            const int my = ly + 1, mx = lx + 1;
+            cls = canny_nms_class(dx, dy, sm[my][mx], sm[my][mx - 1], sm[my][mx + 1], sm[my - 1][mx],
+                                  sm[my + 1][mx], sm[my - 1][mx - 1], sm[my - 1][mx + 1], sm[my + 1][mx - 1],
+                                  sm[my + 1][mx + 1], a.low, a.high);
+        }
+        scls[i] = (uint8_t)(cls == 0 ? 0 : (cls == 2 ? (CLS_CAND | CLS_STRONG) : CLS_CAND));
+        slab[i] = i;
+    }
+    __syncthreads();
+
+    // link inside the tile: W, NW, N, NE
+    for (int i = tid; i < TH * TW; i += NT) {
+        if (!scls[i]) continue;
+        const int ly = i / TW, lx = i - ly * TW;
+        if (lx > 0 && scls[i - 1]) uf_union(slab, i, i - 1);
+        if (ly > 0) {
+            const int up = i - TW;
+            if (lx > 0 && scls[up - 1]) uf_union(slab, i, up - 1);
+            if (scls[up]) uf_union(slab, i, up);
+            if (lx + 1 < TW && scls[up + 1]) uf_union(slab, i, up + 1);
+        }
+    }
+    __syncthreads();
+    // strong pixels mark their tile-local root
+    for (int i = tid; i < TH * TW; i += NT) {
+        if (scls[i] & CLS_STRONG) {
+            const int root = uf_find((volatile int*)slab, i);
+            atomicOr(&sstrong[root >> 5], 1 << (root & 31));
+        }
+    }
+    __syncthreads();
+
+    // write out: class byte (+ root-strong bit) and label = global pixel index of the tile-local root
     uint8_t* map = a.map + (size_t)j.plane * npix;
     int* lab = a.labels + (size_t)j.plane * npix;
-    for (int i = tid; i < TS * TS; i += NT) {
-        const int ly = i / TS, lx = i - ly * TS;
+    for (int i = tid; i < TH * TW; i += NT) {
+        const int ly = i / TW, lx = i - ly * TW;
         const int ry = ty0 + ly, rx = tx0 + lx;
         if (ry >= rows || rx >= cols) continue;
-        const int cy = ly + 2, cx = lx + 2;
-        const int dx = (sg[cy - 1][cx + 1] + 2 * sg[cy][cx + 1] + sg[cy + 1][cx + 1]) -
-                       (sg[cy - 1][cx - 1] + 2 * sg[cy][cx - 1] + sg[cy + 1][cx - 1]);
-        const int dy = (sg[cy + 1][cx - 1] + 2 * sg[cy + 1][cx] + sg[cy + 1][cx + 1]) -
-                       (sg[cy - 1][cx - 1] + 2 * sg[cy - 1][cx] + sg[cy - 1][cx + 1]);
-        const int my = ly + 1, mx = lx + 1;
-        const int cls = canny_nms_class(dx, dy, sm[my][mx], sm[my][mx - 1], sm[my][mx + 1],
-                                        sm[my - 1][mx], sm[my + 1][mx], sm[my - 1][mx - 1],
-                                        sm[my - 1][mx + 1], sm[my + 1][mx - 1], sm[my + 1][mx + 1],
-                                        a.low, a.high);
         const size_t p = (size_t)(j.y0 + ry) * a.W + (j.x0 + rx);
+        int cls = scls[i];
+        if (cls) {
+            const int root = uf_find((volatile int*)slab, i);
+            const int rly = root / TW, rlx = root - rly * TW;
+            lab[p] = (j.y0 + ty0 + rly) * a.W + (j.x0 + tx0 + rlx);
+            if (root == i && ((sstrong[i >> 5] >> (i & 31)) & 1)) cls |= CLS_ROOT_STRONG;
+        }
         map[p] = (uint8_t)cls;
-        if (cls) lab[p] = (int)p;
     }
 
     if (MODE == CANNY_QUADRANTS) {
-        __syncthreads();
         unsigned* gh = a.quad_hist + (size_t)j.out * 768;
         for (int i = tid; i < 768; i += NT) {
             const unsigned v = shist[i];
@@ -158,79 +212,72 @@ __global__ void __launch_bounds__(NT) canny_nms_kernel(CannyArgs a) {
     }
 }
 
-// ---- pass 2: link every candidate with its W, NW, N, NE candidate neighbours (inside the rect)
-__global__ void __launch_bounds__(NT) canny_link_kernel(CannyArgs a) {
+// ---- pass 2: links that cross a tile border.  One thread per border pixel of a tile:
+// top row (TW), left column below it (TH - 1), right column below it (TH - 1).
+__global__ void __launch_bounds__(128) canny_merge_kernel(CannyArgs a) {
     const Job j = make_job(a, blockIdx.z);
     const int rows = j.y1 - j.y0, cols = j.x1 - j.x0;
-    const int ty0 = blockIdx.y * TS, tx0 = blockIdx.x * TS;
+    const int ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
     if (ty0 >= rows || tx0 >= cols) return;
     const size_t npix = (size_t)a.H * a.W;
     const uint8_t* map = a.map + (size_t)j.plane * npix;
     int* lab = a.labels + (size_t)j.plane * npix;
-    for (int i = threadIdx.x; i < TS * TS; i += NT) {
-        const int ly = i / TS, lx = i - ly * TS;
+    for (int i = threadIdx.x; i < TW + 2 * (TH - 1); i += 128) {
+        int ly, lx;
+        if (i < TW) { ly = 0; lx = i; }
+        else if (i < TW + TH - 1) { ly = i - TW + 1; lx = 0; }
+        else { ly = i - (TW + TH - 1) + 1; lx = TW - 1; }
         const int ry = ty0 + ly, rx = tx0 + lx;
         if (ry >= rows || rx >= cols) continue;
-        const int y = j.y0 + ry, x = j.x0 + rx;
-        const int p = y * a.W + x;
+        const int p = (j.y0 + ry) * a.W + (j.x0 + rx);
         if (!map[p]) continue;
-        if (rx > 0 && map[p - 1]) uf_union(lab, p, p - 1);
+        if (lx == 0 && rx > 0 && map[p - 1]) uf_union(lab, p, p - 1);
         if (ry > 0) {
             const int up = p - a.W;
-            if (rx > 0 && map[up - 1]) uf_union(lab, p, up - 1);
-            if (map[up]) uf_union(lab, p, up);
-            if (rx + 1 < cols && map[up + 1]) uf_union(lab, p, up + 1);
+            if ((lx == 0 || ly == 0) && rx > 0 && map[up - 1]) uf_union(lab, p, up - 1);
+            if (ly == 0 && map[up]) uf_union(lab, p, up);
+            if ((ly == 0 || lx == TW - 1) && rx + 1 < cols && map[up + 1]) uf_union(lab, p, up + 1);
         }
     }
 }
 
-// ---- pass 3: strong pixels flag the root of their component (and shorten their own path)
-__global__ void __launch_bounds__(NT) canny_flag_kernel(CannyArgs a) {
+// ---- pass 3 / 4 walk every pixel of the rectangle, 4 pixels of a row per thread
+template <bool COUNT>
+__global__ void __launch_bounds__(NT) canny_resolve_kernel(CannyArgs a) {
     const Job j = make_job(a, blockIdx.z);
     const int rows = j.y1 - j.y0, cols = j.x1 - j.x0;
-    const int ty0 = blockIdx.y * TS, tx0 = blockIdx.x * TS;
-    if (ty0 >= rows || tx0 >= cols) return;
-    const size_t npix = (size_t)a.H * a.W;
-    const uint8_t* map = a.map + (size_t)j.plane * npix;
-    int* lab = a.labels + (size_t)j.plane * npix;
-    for (int i = threadIdx.x; i < TS * TS; i += NT) {
-        const int ly = i / TS, lx = i - ly * TS;
-        const int ry = ty0 + ly, rx = tx0 + lx;
-        if (ry >= rows || rx >= cols) continue;
-        const int p = (j.y0 + ry) * a.W + (j.x0 + rx);
-        if (map[p] != 2) continue;
-        const int root = uf_find(lab, p);
-        atomicOr(&lab[root], LABEL_FLAG);
-    }
-}
-
-// ---- pass 4: count candidates whose root is flagged
-__global__ void __launch_bounds__(NT) canny_count_kernel(CannyArgs a) {
-    const Job j = make_job(a, blockIdx.z);
-    const int rows = j.y1 - j.y0, cols = j.x1 - j.x0;
-    const int ty0 = blockIdx.y * TS, tx0 = blockIdx.x * TS;
+    const int ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
     if (ty0 >= rows || tx0 >= cols) return;
     const size_t npix = (size_t)a.H * a.W;
     const uint8_t* map = a.map + (size_t)j.plane * npix;
     int* lab = a.labels + (size_t)j.plane * npix;
     unsigned cnt = 0;
-    for (int i = threadIdx.x; i < TS * TS; i += NT) {
-        const int ly = i / TS, lx = i - ly * TS;
+    for (int i = threadIdx.x; i < TH * TW; i += NT) {
+        const int ly = i / TW, lx = i - ly * TW;
         const int ry = ty0 + ly, rx = tx0 + lx;
         if (ry >= rows || rx >= cols) continue;
         const int p = (j.y0 + ry) * a.W + (j.x0 + rx);
-        if (!map[p]) continue;
-        const int root = uf_find(lab, p);
-        if (lab[root] & LABEL_FLAG) ++cnt;
+        const int cls = map[p];
+        if (COUNT) {
+            if (!cls) continue;
+            const int root = uf_find((volatile int*)lab, p);
+            if (lab[root] & LABEL_FLAG) ++cnt;
+        } else {
+            if (!(cls & CLS_ROOT_STRONG)) continue;
+            const int root = uf_find((volatile int*)lab, p);
+            atomicOr(&lab[root], LABEL_FLAG);
+        }
     }
-    cnt = warp_sum_u32(cnt);
-    __shared__ unsigned sw[NT / 32];
-    if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = cnt;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned t = 0;
-        for (int w = 0; w < NT / 32; ++w) t += sw[w];
-        if (t) atomicAdd(&a.counts[j.out], t);
+    if (COUNT) {
+        cnt = warp_sum_u32(cnt);
+        __shared__ unsigned sw[NT / 32];
+        if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = cnt;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned t = 0;
+            for (int w = 0; w < NT / 32; ++w) t += sw[w];
+            if (t) atomicAdd(&a.counts[j.out], t);
+        }
     }
 }
 
@@ -238,13 +285,14 @@ __global__ void __launch_bounds__(NT) canny_count_kernel(CannyArgs a) {
 
 int launch_canny(const CannyArgs& a, int max_rows, int max_cols, int instances, cudaStream_t st) {
     if (max_rows <= 0 || max_cols <= 0 || instances <= 0) return 0;
-    dim3 grid((max_cols + TS - 1) / TS, (max_rows + TS - 1) / TS, instances);
-    if (a.mode == CANNY_QUADRANTS) canny_nms_kernel<CANNY_QUADRANTS><<<grid, NT, 0, st>>>(a);
-    else canny_nms_kernel<CANNY_PLANES><<<grid, NT, 0, st>>>(a);
-    canny_link_kernel<<<grid, NT, 0, st>>>(a);
-    canny_flag_kernel<<<grid, NT, 0, st>>>(a);
-    canny_count_kernel<<<grid, NT, 0, st>>>(a);
-    return 4;
+    dim3 grid((max_cols + TW - 1) / TW, (max_rows + TH - 1) / TH, instances);
+    if (a.mode == CANNY_QUADRANTS) canny_tile_kernel<CANNY_QUADRANTS><<<grid, NT, 0, st>>>(a);
+    else canny_tile_kernel<CANNY_PLANES><<<grid, NT, 0, st>>>(a);
+    int launches = 3;
+    if (grid.x > 1 || grid.y > 1) { canny_merge_kernel<<<grid, 128, 0, st>>>(a); ++launches; }
+    canny_resolve_kernel<false><<<grid, NT, 0, st>>>(a);
+    canny_resolve_kernel<true><<<grid, NT, 0, st>>>(a);
+    return launches;
 }
 
 }  // namespace uwie
