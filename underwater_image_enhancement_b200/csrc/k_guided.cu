@@ -277,9 +277,9 @@ __global__ void __launch_bounds__(GNT) gf_recover_kernel(GuidedArgs a) {
                 const T v2 = clip01<T>((T)__dadd_rn(q2, dl2));
                 T* o = out + (ro + x) * 3;
                 o[0] = v0; o[1] = v1; o[2] = v2;
-                atomicAdd(&shist[0 * kSelBinsA + (sel_key<T>(v0) >> 21)], 1u);
-                atomicAdd(&shist[1 * kSelBinsA + (sel_key<T>(v1) >> 21)], 1u);
-                atomicAdd(&shist[2 * kSelBinsA + (sel_key<T>(v2) >> 21)], 1u);
+                atomicAdd(&shist[0 * kSelBinsA + sel_bin_a<T>(v0)], 1u);
+                atomicAdd(&shist[1 * kSelBinsA + sel_bin_a<T>(v1)], 1u);
+                atomicAdd(&shist[2 * kSelBinsA + sel_bin_a<T>(v2)], 1u);
             }
             __syncwarp();
             row_sub(yo - s.lo);

@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
         rank = target_rank(rc, a.n, tg & 7);
         if (lane == 0) { T.active = rank >= 0; T.prefix = 0; T.rank = rank; T.rep = tg; }
     } else {
-        rank = T.active ? T.rank : -1;
+        rank = T.active == 1 ? T.rank : -1;
     }
     __syncwarp();
     if (rank >= 0) {
@@ -80,7 +80,12 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
             acc = nx;
         }
         T.rank = rank - acc;
-        T.prefix = LEVEL == 0 ? (unsigned)bin : ((T.prefix << bits) | (unsigned)bin);
+        if (LEVEL == 0) {
+            // bin 0 of level A holds the exact zeros (clipping makes them very common): resolved at once
+            if (bin == 0) T.active = 2; else T.prefix = (unsigned)(bin - 1);
+        } else {
+            T.prefix = (T.prefix << bits) | (unsigned)bin;
+        }
     }
     }
     // targets of one channel that sit in the same bin share one histogram at the next level:
@@ -88,10 +93,10 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
     __syncthreads();
     if (lane == 0) {
         int rep = tg;
-        if (T.active) {
+        if (T.active == 1) {
             for (int o = (tg & ~7); o < tg; ++o) {
                 const SelTarget& O = a.targets[(size_t)inst * kSelTargets + o];
-                if (O.active && O.prefix == T.prefix) { rep = o; break; }
+                if (O.active == 1 && O.prefix == T.prefix) { rep = o; break; }
             }
         }
         T.rep = rep;
@@ -111,7 +116,7 @@ __device__ __forceinline__ bool pass_prologue(const SelectArgs& a, int inst, Pas
     __syncthreads();
     if (threadIdx.x < kSelTargets) {
         const SelTarget& t = a.targets[(size_t)inst * kSelTargets + threadIdx.x];
-        int on = t.active;
+        int on = t.active == 1;
         if (only_inexact && t.prefix >= kExactKeyMin) on = 0;     // float32 value already exact
         if (t.rep != (int)threadIdx.x) on = 0;                     // rides on its representative's histogram
         ps.pre[threadIdx.x] = t.prefix;
@@ -148,13 +153,14 @@ __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
         bool hot = false;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            key[c] = in ? sel_key<T>(src[px * 3 + c]) : 0u;
-            hot |= in && ps.hot[c][key[c] >> 21];
+            const T x = in ? src[px * 3 + c] : (T)0;
+            key[c] = x != (T)0 ? sel_key<T>(x) : 0xffffffffu;   // exact zeros live in level-A bin 0, not here
+            hot |= (key[c] >> 21) <= 1024u ? ps.hot[c][key[c] >> 21] != 0 : false;
         }
         if (__ballot_sync(0xffffffffu, hot) == 0) continue;     // the common case
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            const bool hc = in && ps.hot[c][key[c] >> 21];
+            const bool hc = (key[c] >> 21) <= 1024u ? ps.hot[c][key[c] >> 21] != 0 : false;
             if (__ballot_sync(0xffffffffu, hc) == 0) continue;
             const unsigned hi = key[c] >> SHIFT, sub = (key[c] >> SUBSHIFT) & SUBMASK;
             for (int t = 0; t < 8; ++t) {
@@ -200,13 +206,13 @@ __global__ void __launch_bounds__(NT) sel_table_kernel(SelectArgs a) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             x[c] = in ? src[px * 3 + c] : (T)0;
-            key[c] = sel_key<T>(x[c]);
-            hot |= in && ps.hot[c][key[c] >> 21];
+            key[c] = x[c] != (T)0 ? sel_key<T>(x[c]) : 0xffffffffu;
+            hot |= (key[c] >> 21) <= 1024u ? ps.hot[c][key[c] >> 21] != 0 : false;
         }
         if (__ballot_sync(0xffffffffu, hot) == 0) continue;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            const bool hc = in && ps.hot[c][key[c] >> 21];
+            const bool hc = (key[c] >> 21) <= 1024u ? ps.hot[c][key[c] >> 21] != 0 : false;
             if (__ballot_sync(0xffffffffu, hc) == 0) continue;
             const unsigned long long bits = sel_bits<T>(x[c]);
             for (int t = 0; t < 8; ++t) {
@@ -239,6 +245,7 @@ __global__ void __launch_bounds__(NT) sel_finish_kernel(SelectArgs a) {
     for (int tg = 0; tg < kSelTargets; ++tg) {
         const SelTarget t = a.targets[(size_t)inst * kSelTargets + tg];
         if (!t.active) continue;                       // uniform per block
+        if (t.active == 2) { if (threadIdx.x == 0) s_val[tg] = 0.0; continue; }
         if (sizeof(T) == 4 && t.prefix >= kExactKeyMin) {
             // key = x * 2^31 exactly, with at most 24 significant bits
             if (threadIdx.x == 0) s_val[tg] = (double)__fmul_rn(__uint2float_rn(t.prefix), 4.656612873077393e-10f);

@@ -4,6 +4,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -68,8 +69,16 @@ struct uwie_engine {
     struct Mark { const char* name; cudaEvent_t ev; int kernels; };
     std::vector<Mark> marks;
     std::vector<cudaEvent_t> ev_pool;
-    // pinned staging for the host entry point
-    uint8_t* pin_frames = nullptr;
+    // two-slot pipeline of the host entry point
+    struct HostPipe {
+        bool ready = false;
+        cudaStream_t s_in = nullptr, s_out = nullptr;
+        cudaEvent_t ev_in[2] = {}, ev_run[2] = {}, ev_out[2] = {}, ev_start = nullptr;
+        uint8_t* frames[2] = {}; uint8_t* best_img[2] = {}; uint8_t* out_all[2] = {}; char* small[2] = {};
+        // pinned landing zone of the small results: a D2H copy into PAGEABLE memory blocks the host
+        // until the stream gets there, which would serialise the whole pipeline
+        char* h_small = nullptr; size_t h_small_frames = 0;
+    } pipe;
     template <class T> T* at(size_t off) const { return reinterpret_cast<T*>(ws + off); }
 };
 
@@ -302,7 +311,22 @@ int uwie_engine_create(uwie_engine** out, const uwie_library* lib, const uwie_st
 void uwie_engine_destroy(uwie_engine* e) {
     if (!e) return;
     if (e->owns_ws && e->ws) cudaFree(e->ws);
-    if (e->pin_frames) cudaFree(e->pin_frames);
+    {
+        auto& hp = e->pipe;
+        for (int k = 0; k < 2; ++k) {
+            if (hp.frames[k]) cudaFree(hp.frames[k]);
+            if (hp.best_img[k]) cudaFree(hp.best_img[k]);
+            if (hp.out_all[k]) cudaFree(hp.out_all[k]);
+            if (hp.small[k]) cudaFree(hp.small[k]);
+            if (hp.ev_in[k]) cudaEventDestroy(hp.ev_in[k]);
+            if (hp.ev_run[k]) cudaEventDestroy(hp.ev_run[k]);
+            if (hp.ev_out[k]) cudaEventDestroy(hp.ev_out[k]);
+        }
+        if (hp.ev_start) cudaEventDestroy(hp.ev_start);
+        if (hp.h_small) cudaFreeHost(hp.h_small);
+        if (hp.s_in) cudaStreamDestroy(hp.s_in);
+        if (hp.s_out) cudaStreamDestroy(hp.s_out);
+    }
     for (auto& m : e->marks) cudaEventDestroy(m.ev);
     for (auto& ev : e->ev_pool) cudaEventDestroy(ev);
     delete e;
@@ -403,7 +427,12 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         ga.B = batch; ga.S = S; ga.H = H; ga.W = W; ga.lib = e->lib; ga.recipes = sa.recipes;
         ga.n_dehaze = e->n_dehaze;
         for (int i = 0; i < kStrategiesMax; ++i) ga.dehaze_idx[i] = e->dehaze_idx[i];
-        ga.rows_per_block = H >= 512 ? (H + 7) / 8 : (H >= 128 ? (H + 1) / 2 : H);
+        {
+            // row chunks: more chunks = more warps in flight, but each chunk re-reads r - 1 warm-up rows
+            int chunks = H >= 512 ? 12 : (H >= 128 ? 2 : 1);
+            if (const char* ev = std::getenv("UWIE_GF_CHUNKS")) { const int v = std::atoi(ev); if (v >= 1 && v <= H) chunks = v; }
+            ga.rows_per_block = (H + chunks - 1) / chunks;
+        }
         ga.gray_plane = e->at<uint8_t>(L.gf_gray); ga.dark_plane = e->at<float>(L.gf_dark);
         ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;
         ga.ab = e->at<double>(L.ab); ga.recovered = e->at<void>(L.recovered);
@@ -509,41 +538,90 @@ int uwie_engine_check(uwie_engine* e, void* stream) {
     return UWIE_OK;
 }
 
+// Host entry point: a two-slot pipeline.  Slot k owns device copies of a chunk's frames and of
+// every result; the H2D copy of chunk i+1 and the D2H copies of chunk i-1 run on their own streams
+// while the kernels of chunk i run on the caller's stream (the workspace is single, so kernels of
+// different chunks never overlap each other).  With pinned host buffers the copies are truly
+// asynchronous; with pageable ones CUDA stages them and the result is the same, only slower.
 int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int count, uint8_t* out_all_host,
                             uint8_t* out_best_host, double* scores_host, int32_t* best_host,
                             int32_t* type_host, float* light_host, void* stream) {
     if (!e || !frames_host) return fail(UWIE_ERR_ARG, "null engine or frames");
     if (count < 1) return fail(UWIE_ERR_ARG, "count must be positive");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const size_t N = (size_t)e->H * e->W, S = e->S;
-    // device-side staging, allocated on first use and kept
-    if (!e->pin_frames) {
-        // layout: frames | out_best | types | light   (scores, best and out_all live in the workspace)
-        const size_t bytes = (size_t)e->B * (N * 3 * 2 + 4 + 12) + 1024;
-        void* p = nullptr;
-        CU(cudaMalloc(&p, bytes));
-        e->pin_frames = static_cast<uint8_t*>(p);
+    const size_t N = (size_t)e->H * e->W, S = e->S, B = e->B;
+    uwie_engine::HostPipe& hp = e->pipe;
+    if (!hp.ready) {
+        CU(cudaStreamCreateWithFlags(&hp.s_in, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&hp.s_out, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            CU(cudaEventCreateWithFlags(&hp.ev_in[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&hp.ev_run[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&hp.ev_out[k], cudaEventDisableTiming));
+            CU(cudaMalloc(&hp.frames[k], B * N * 3));
+            CU(cudaMalloc(&hp.best_img[k], B * N * 3));
+            CU(cudaMalloc(&hp.small[k], B * (S * kScoreCols * 8 + 4 + 4 + 12) + 256));
+        }
+        CU(cudaEventCreateWithFlags(&hp.ev_start, cudaEventDisableTiming));
+        hp.ready = true;
     }
-    uint8_t* d_frames = e->pin_frames;
-    uint8_t* d_best_img = d_frames + (size_t)e->B * N * 3;
-    int32_t* d_types = reinterpret_cast<int32_t*>(d_best_img + (size_t)e->B * N * 3);
-    float* d_light = reinterpret_cast<float*>(d_types + e->B);
-    for (int done = 0; done < count; done += e->B) {
-        const int nb = count - done < e->B ? count - done : e->B;
-        CU(cudaMemcpyAsync(d_frames, frames_host + (size_t)done * N * 3, (size_t)nb * N * 3, cudaMemcpyHostToDevice, st));
-        int rc = enqueue_batch(e, d_frames, nb, nullptr, out_best_host ? d_best_img : nullptr, nullptr, nullptr,
-                               d_types, d_light, st);
+    // out_all of both slots is allocated only if somebody asks for it (it is S times a chunk)
+    if (out_all_host && !hp.out_all[0]) {
+        for (int k = 0; k < 2; ++k) CU(cudaMalloc(&hp.out_all[k], B * S * N * 3));
+    }
+    const size_t rec_bytes = S * kScoreCols * 8 + 4 + 4 + 12;
+    if (hp.h_small_frames < (size_t)count) {
+        if (hp.h_small) cudaFreeHost(hp.h_small);
+        hp.h_small = nullptr; hp.h_small_frames = 0;
+        CU(cudaMallocHost(&hp.h_small, (size_t)count * rec_bytes + 64));
+        hp.h_small_frames = count;
+    }
+    double* p_scores = reinterpret_cast<double*>(hp.h_small);
+    int32_t* p_best = reinterpret_cast<int32_t*>(p_scores + (size_t)count * S * kScoreCols);
+    int32_t* p_types = p_best + count;
+    float* p_light = reinterpret_cast<float*>(p_types + count);
+    // the copy streams must not start before work already queued on the caller's stream
+    CU(cudaEventRecord(hp.ev_start, st));
+    CU(cudaStreamWaitEvent(hp.s_in, hp.ev_start, 0));
+    CU(cudaStreamWaitEvent(hp.s_out, hp.ev_start, 0));
+    int chunk = 0;
+    for (int done = 0; done < count; done += (int)B, ++chunk) {
+        const int k = chunk & 1;
+        const int nb = count - done < (int)B ? count - done : (int)B;
+        double* d_scores = reinterpret_cast<double*>(hp.small[k]);
+        int32_t* d_best = reinterpret_cast<int32_t*>(d_scores + B * S * kScoreCols);
+        int32_t* d_types = d_best + B;
+        float* d_light = reinterpret_cast<float*>(d_types + B);
+        // H2D: the slot's frames are free once the kernels of chunk - 2 are done
+        if (chunk >= 2) CU(cudaStreamWaitEvent(hp.s_in, hp.ev_run[k], 0));
+        CU(cudaMemcpyAsync(hp.frames[k], frames_host + (size_t)done * N * 3, (size_t)nb * N * 3,
+                           cudaMemcpyHostToDevice, hp.s_in));
+        CU(cudaEventRecord(hp.ev_in[k], hp.s_in));
+        // kernels: need the frames, and the slot's result buffers drained (D2H of chunk - 2)
+        CU(cudaStreamWaitEvent(st, hp.ev_in[k], 0));
+        if (chunk >= 2) CU(cudaStreamWaitEvent(st, hp.ev_out[k], 0));
+        int rc = enqueue_batch(e, hp.frames[k], nb, out_all_host ? hp.out_all[k] : nullptr,
+                               out_best_host ? hp.best_img[k] : nullptr, d_scores, d_best, d_types, d_light, st);
         if (rc) return rc;
+        CU(cudaEventRecord(hp.ev_run[k], st));
+        // D2H
+        CU(cudaStreamWaitEvent(hp.s_out, hp.ev_run[k], 0));
         if (out_all_host)
-            CU(cudaMemcpyAsync(out_all_host + (size_t)done * S * N * 3, e->ws + e->L.out, (size_t)nb * S * N * 3, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(out_all_host + (size_t)done * S * N * 3, hp.out_all[k], (size_t)nb * S * N * 3, cudaMemcpyDeviceToHost, hp.s_out));
         if (out_best_host)
-            CU(cudaMemcpyAsync(out_best_host + (size_t)done * N * 3, d_best_img, (size_t)nb * N * 3, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(out_best_host + (size_t)done * N * 3, hp.best_img[k], (size_t)nb * N * 3, cudaMemcpyDeviceToHost, hp.s_out));
         if (scores_host)
-            CU(cudaMemcpyAsync(scores_host + (size_t)done * S * kScoreCols, e->ws + e->L.scores, sizeof(double) * nb * S * kScoreCols, cudaMemcpyDeviceToHost, st));
-        if (best_host) CU(cudaMemcpyAsync(best_host + done, e->ws + e->L.best, sizeof(int) * nb, cudaMemcpyDeviceToHost, st));
-        if (type_host) CU(cudaMemcpyAsync(type_host + done, d_types, sizeof(int) * nb, cudaMemcpyDeviceToHost, st));
-        if (light_host) CU(cudaMemcpyAsync(light_host + (size_t)done * 3, d_light, sizeof(float) * nb * 3, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(p_scores + (size_t)done * S * kScoreCols, d_scores, sizeof(double) * nb * S * kScoreCols, cudaMemcpyDeviceToHost, hp.s_out));
+        if (best_host) CU(cudaMemcpyAsync(p_best + done, d_best, sizeof(int) * nb, cudaMemcpyDeviceToHost, hp.s_out));
+        if (type_host) CU(cudaMemcpyAsync(p_types + done, d_types, sizeof(int) * nb, cudaMemcpyDeviceToHost, hp.s_out));
+        if (light_host) CU(cudaMemcpyAsync(p_light + (size_t)done * 3, d_light, sizeof(float) * nb * 3, cudaMemcpyDeviceToHost, hp.s_out));
+        CU(cudaEventRecord(hp.ev_out[k], hp.s_out));
     }
+    CU(cudaStreamSynchronize(hp.s_out));
+    if (scores_host) std::memcpy(scores_host, p_scores, sizeof(double) * (size_t)count * S * kScoreCols);
+    if (best_host) std::memcpy(best_host, p_best, sizeof(int) * (size_t)count);
+    if (type_host) std::memcpy(type_host, p_types, sizeof(int) * (size_t)count);
+    if (light_host) std::memcpy(light_host, p_light, sizeof(float) * (size_t)count * 3);
     return uwie_engine_check(e, stream);
 }
 
