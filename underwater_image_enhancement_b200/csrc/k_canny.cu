@@ -72,6 +72,15 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b) {
     } while (!done);
 }
 
+__device__ __forceinline__ unsigned long long row_mask(const unsigned* m) {
+    return (unsigned long long)m[0] | ((unsigned long long)m[1] << 32);
+}
+// first pixel of the run of set bits of `m` that contains bit x
+__device__ __forceinline__ int run_start(unsigned long long m, int x) {
+    const unsigned long long below = ~m & ((1ull << x) - 1ull);
+    return below ? 64 - __clzll((long long)below) : 0;
+}
+
 // ---- pass 1
 template <int MODE>
 __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
@@ -82,7 +91,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
 
     __shared__ uint8_t sg[TH + 4][TW + 4];
     __shared__ uint16_t sm[TH + 2][TW + 2];
-    __shared__ uint8_t scls[TH * TW];
+    __shared__ unsigned smask_c[TH][2], smask_s[TH][2];   // per tile row: candidate / strong bit masks
     __shared__ int slab[TH * TW];
     __shared__ int sstrong[TH * TW / 32];          // bit per tile pixel: root of a component with a strong pixel
     __shared__ unsigned shist[MODE == CANNY_QUADRANTS ? 768 : 1];
@@ -142,8 +151,10 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     }
     __syncthreads();
 
-    // classification; every candidate starts as its own component
-    for (int i = tid; i < TH * TW; i += NT) {
+    // classification.  Thread mapping: 8 passes, in each a warp owns half a tile row, so one ballot
+    // gives the candidate / strong bit masks of that half row.
+    for (int it = 0; it < TH * TW / NT; ++it) {
+        const int i = it * NT + tid;
         const int ly = i / TW, lx = i - ly * TW;
         const int ry = ty0 + ly, rx = tx0 + lx;
         int cls = 0;
@@ -158,27 +169,44 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
                                   sm[my + 1][mx], sm[my - 1][mx - 1], sm[my - 1][mx + 1], sm[my + 1][mx - 1],
                                   sm[my + 1][mx + 1], a.low, a.high);
         }
-        scls[i] = (uint8_t)(cls == 0 ? 0 : (cls == 2 ? (CLS_CAND | CLS_STRONG) : CLS_CAND));
+        const unsigned mc = __ballot_sync(0xffffffffu, cls != 0);
+        const unsigned ms = __ballot_sync(0xffffffffu, cls == 2);
+        if ((tid & 31) == 0) { smask_c[ly][lx >> 5] = mc; smask_s[ly][lx >> 5] = ms; }
         slab[i] = i;
     }
     __syncthreads();
 
-    // link inside the tile: W, NW, N, NE
-    for (int i = tid; i < TH * TW; i += NT) {
-        if (!scls[i]) continue;
+    // Link inside the tile.  A horizontal run of candidates is one node (its first pixel); runs of
+    // neighbouring rows are united once per contact: with U the row above,
+    //   up set:            unite unless both W and NW are set (then the pixel to the left did it)
+    //   up clear, NW set:  unite if W is clear          up clear, NE set:  unite if E is clear
+    for (int it = 0; it < TH * TW / NT; ++it) {
+        const int i = it * NT + tid;
         const int ly = i / TW, lx = i - ly * TW;
-        if (lx > 0 && scls[i - 1]) uf_union(slab, i, i - 1);
-        if (ly > 0) {
-            const int up = i - TW;
-            if (lx > 0 && scls[up - 1]) uf_union(slab, i, up - 1);
-            if (scls[up]) uf_union(slab, i, up);
-            if (lx + 1 < TW && scls[up + 1]) uf_union(slab, i, up + 1);
+        if (ly == 0) continue;                                                  // warp-uniform
+        const unsigned long long R = row_mask(smask_c[ly]), U = row_mask(smask_c[ly - 1]);
+        if (!((R >> lx) & 1ull) || U == 0ull) continue;
+        const bool up = (U >> lx) & 1ull;
+        const bool nw = lx > 0 && ((U >> (lx - 1)) & 1ull), ne = lx < TW - 1 && ((U >> (lx + 1)) & 1ull);
+        const bool w = lx > 0 && ((R >> (lx - 1)) & 1ull), e = lx < TW - 1 && ((R >> (lx + 1)) & 1ull);
+        const int me = ly * TW + run_start(R, lx);
+        if (up) { if (!w || !nw) uf_union(slab, me, (ly - 1) * TW + run_start(U, lx)); }
+        else {
+            if (nw && !w) uf_union(slab, me, (ly - 1) * TW + run_start(U, lx - 1));
+            if (ne && !e) uf_union(slab, me, (ly - 1) * TW + lx + 1);           // NE starts its run (up is clear)
         }
     }
     __syncthreads();
-    // strong pixels mark their tile-local root
-    for (int i = tid; i < TH * TW; i += NT) {
-        if (scls[i] & CLS_STRONG) {
+    // a run that holds a strong pixel marks its root (done by the run's first pixel)
+    for (int it = 0; it < TH * TW / NT; ++it) {
+        const int i = it * NT + tid;
+        const int ly = i / TW, lx = i - ly * TW;
+        const unsigned long long R = row_mask(smask_c[ly]);
+        if (!((R >> lx) & 1ull) || (lx > 0 && ((R >> (lx - 1)) & 1ull))) continue;   // not a run start
+        const unsigned long long holes = ~R & (~0ull << lx);
+        const int end = holes ? __ffsll((long long)holes) - 1 : TW;               // first clear bit after the run
+        const unsigned long long run = (end >= 64 ? ~0ull : ((1ull << end) - 1)) & (~0ull << lx);
+        if (row_mask(smask_s[ly]) & run) {
             const int root = uf_find((volatile int*)slab, i);
             atomicOr(&sstrong[root >> 5], 1 << (root & 31));
         }
@@ -188,14 +216,17 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     // write out: class byte (+ root-strong bit) and label = global pixel index of the tile-local root
     uint8_t* map = a.map + (size_t)j.plane * npix;
     int* lab = a.labels + (size_t)j.plane * npix;
-    for (int i = tid; i < TH * TW; i += NT) {
+    for (int it = 0; it < TH * TW / NT; ++it) {
+        const int i = it * NT + tid;
         const int ly = i / TW, lx = i - ly * TW;
         const int ry = ty0 + ly, rx = tx0 + lx;
         if (ry >= rows || rx >= cols) continue;
         const size_t p = (size_t)(j.y0 + ry) * a.W + (j.x0 + rx);
-        int cls = scls[i];
-        if (cls) {
-            const int root = uf_find((volatile int*)slab, i);
+        const unsigned long long R = row_mask(smask_c[ly]);
+        int cls = 0;
+        if ((R >> lx) & 1ull) {
+            cls = CLS_CAND | (((row_mask(smask_s[ly]) >> lx) & 1ull) ? CLS_STRONG : 0);
+            const int root = uf_find((volatile int*)slab, ly * TW + run_start(R, lx));
             const int rly = root / TW, rlx = root - rly * TW;
             lab[p] = (j.y0 + ty0 + rly) * a.W + (j.x0 + tx0 + rlx);
             if (root == i && ((sstrong[i >> 5] >> (i & 31)) & 1)) cls |= CLS_ROOT_STRONG;
