@@ -5,7 +5,7 @@
 // BORDER_REFLECT_101, scale applied as a multiplication by 1/(r*r).
 //
 // Three kernels:
-//   gf_prep_kernel      frame bytes -> gray plane (uint8) and dark-channel plane (float32), per frame
+//   gf_prep_kernel      frame bytes -> packed (R, G, B, gray) word plane and dark-channel plane (float32), per frame
 //   gf_ab_kernel        gray, dark -> box sums of I, p, I*p, I*I -> a, b (float64 planes)
 //   gf_recover_kernel   a, b -> mean_a * I + mean_b -> t -> (img - A)/t + A -> recovered frame
 //                       (+ the first level of the percentile histograms, see k_select.cu)
@@ -44,11 +44,12 @@ __global__ void __launch_bounds__(256) gf_prep_kernel(GuidedArgs a) {
     __syncthreads();
     const size_t npix = (size_t)a.H * a.W;
     const uint8_t* f = a.frames + (size_t)b * npix * 3;
-    uint8_t* gp = a.gray_plane + (size_t)b * npix;
+    unsigned* gp = a.pix_plane + (size_t)b * npix;
     float* dp = a.dark_plane + (size_t)b * npix;
     for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < npix; i += (size_t)gridDim.x * 256) {
-        const int r = f[i * 3], g = f[i * 3 + 1], bl = f[i * 3 + 2];
-        gp[i] = (uint8_t)gray_q15(sq[0][r], sq[1][g], sq[2][bl]);
+        const unsigned r = f[i * 3], g = f[i * 3 + 1], bl = f[i * 3 + 2];
+        const unsigned gq = (unsigned)gray_q15(sq[0][r], sq[1][g], sq[2][bl]);
+        gp[i] = r | (g << 8) | (bl << 16) | (gq << 24);      // one aligned word per pixel for the marching kernels
         dp[i] = fminf(fminf(sdiv[0][r], sdiv[1][g]), sdiv[2][bl]);
     }
 }
@@ -76,7 +77,7 @@ __device__ __forceinline__ Strip make_strip(const GuidedArgs& a, int r) {
 }
 
 // ------------------------------------------------------------------ a, b
-__global__ void __launch_bounds__(GNT) gf_ab_kernel(GuidedArgs a) {
+__global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
     __shared__ double sP[GWARPS][GSPAN];
     __shared__ double sGP[GWARPS][GSPAN];
     __shared__ unsigned long long sG[GWARPS][GSPAN];     // (sum g) << 32 | sum g*g
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(GNT) gf_ab_kernel(GuidedArgs a) {
     const int clip_t0 = a.lib.clip_t0;
     const double eps = rc.eps;
     const size_t npix = (size_t)a.H * a.W;
-    const uint8_t* gray = a.gray_plane + (size_t)b * npix;
+    const unsigned* pix = a.pix_plane + (size_t)b * npix;
     const float* dark = a.dark_plane + (size_t)b * npix;
     double* pa = a.ab + (size_t)inst * 2 * npix;
     double* pb = pa + npix;
@@ -106,31 +107,35 @@ __global__ void __launch_bounds__(GNT) gf_ab_kernel(GuidedArgs a) {
 #pragma unroll
     for (int j = 0; j < GC; ++j) { vp[j] = 0.0; vgp[j] = 0.0; vg[j] = 0ull; }
 
-    auto row_add = [&](int yy) {
+    // Row loads are software-pipelined: the values of the row that enters (leaves) the window in the
+    // NEXT step are requested right after this step's were consumed, so their latency hides behind
+    // the shared-memory phase instead of stalling a warp that has nothing else to do.
+    unsigned gE[GC], gL[GC];
+    float dE[GC], dL[GC];
+    auto row_load = [&](int yy, unsigned* g, float* d) {
         const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
 #pragma unroll
-        for (int j = 0; j < GC; ++j) {
-            const unsigned g = gray[ro + cx[j]];
-            const double p = (double)transmission0(omega, clip_t0, dark[ro + cx[j]]);
-            vp[j] += p; vgp[j] += (double)g * p;
-            vg[j] += ((unsigned long long)g << 32) | (unsigned long long)(g * g);
-        }
+        for (int j = 0; j < GC; ++j) { g[j] = pix[ro + cx[j]] >> 24; d[j] = dark[ro + cx[j]]; }
     };
-    auto row_sub = [&](int yy) {
-        const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+    auto row_acc = [&](const unsigned* gq, const float* d, bool add) {
 #pragma unroll
         for (int j = 0; j < GC; ++j) {
-            const unsigned g = gray[ro + cx[j]];
-            const double p = (double)transmission0(omega, clip_t0, dark[ro + cx[j]]);
-            vp[j] -= p; vgp[j] -= (double)g * p;
-            vg[j] -= ((unsigned long long)g << 32) | (unsigned long long)(g * g);
+            const unsigned g = gq[j];
+            const double p = (double)transmission0(omega, clip_t0, d[j]);
+            const unsigned long long q = ((unsigned long long)g << 32) | (unsigned long long)(g * g);
+            if (add) { vp[j] += p; vgp[j] += (double)g * p; vg[j] += q; }
+            else { vp[j] -= p; vgp[j] -= (double)g * p; vg[j] -= q; }
         }
     };
+    auto row_add = [&](int yy) { row_load(yy, gE, dE); row_acc(gE, dE, true); };
 
     for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) row_add(yy);
     const int base = s.lane * GC;
+    row_load(s.ys + s.hi, gE, dE);
+    row_load(s.ys - s.lo, gL, dL);
     for (int yo = s.ys; yo < s.ye; ++yo) {
-        row_add(yo + s.hi);
+        row_acc(gE, dE, true);
+        if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, gE, dE);
 #pragma unroll
         for (int j = 0; j < GC; ++j) {
             wP[s.lane + 32 * j] = vp[j]; wGP[s.lane + 32 * j] = vgp[j]; wG[s.lane + 32 * j] = vg[j];
@@ -170,13 +175,14 @@ __global__ void __launch_bounds__(GNT) gf_ab_kernel(GuidedArgs a) {
             if (x < a.W) { pa[ro + x] = wP[i]; pb[ro + x] = wGP[i]; }
         }
         __syncwarp();
-        row_sub(yo - s.lo);
+        row_acc(gL, dL, false);
+        if (yo + 1 < s.ye) row_load(yo + 1 - s.lo, gL, dL);
     }
 }
 
 // ------------------------------------------------------------------ recover
 template <class T>
-__global__ void __launch_bounds__(GNT) gf_recover_kernel(GuidedArgs a) {
+__global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
     __shared__ double sA[GWARPS][GSPAN];
     __shared__ double sB[GWARPS][GSPAN];
     __shared__ double sI[256];                 // g / 255.0
@@ -199,8 +205,7 @@ __global__ void __launch_bounds__(GNT) gf_recover_kernel(GuidedArgs a) {
     const Strip s = make_strip(a, rc.radius);
     if (s.valid) {
         const size_t npix = (size_t)a.H * a.W;
-        const uint8_t* frame = a.frames + (size_t)b * npix * 3;
-        const uint8_t* gray = a.gray_plane + (size_t)b * npix;
+        const unsigned* pix = a.pix_plane + (size_t)b * npix;
         const double* pa = a.ab + (size_t)inst * 2 * npix;
         const double* pb = pa + npix;
         T* out = reinterpret_cast<T*>(a.recovered) + (size_t)inst * npix * 3;
@@ -214,20 +219,33 @@ __global__ void __launch_bounds__(GNT) gf_recover_kernel(GuidedArgs a) {
         double va[GC], vb[GC];
 #pragma unroll
         for (int j = 0; j < GC; ++j) { va[j] = 0.0; vb[j] = 0.0; }
-        auto row_add = [&](int yy) {
+        double aE[GC], bE[GC], aL[GC], bL[GC];           // software-pipelined row loads (see gf_ab_kernel)
+        auto row_load = [&](int yy, double* qa, double* qb) {
             const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] += pa[ro + cx[j]]; vb[j] += pb[ro + cx[j]]; }
+            for (int j = 0; j < GC; ++j) { qa[j] = pa[ro + cx[j]]; qb[j] = pb[ro + cx[j]]; }
         };
-        auto row_sub = [&](int yy) {
-            const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+        auto row_add = [&](int yy) {
+            row_load(yy, aE, bE);
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] -= pa[ro + cx[j]]; vb[j] -= pb[ro + cx[j]]; }
+            for (int j = 0; j < GC; ++j) { va[j] += aE[j]; vb[j] += bE[j]; }
         };
         for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) row_add(yy);
         const int base = s.lane * GC;
+        row_load(s.ys + s.hi, aE, bE);
+        row_load(s.ys - s.lo, aL, bL);
         for (int yo = s.ys; yo < s.ye; ++yo) {
-            row_add(yo + s.hi);
+#pragma unroll
+            for (int j = 0; j < GC; ++j) { va[j] += aE[j]; vb[j] += bE[j]; }
+            if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, aE, bE);
+            // this row's pixels (frame bytes + gray) for the recovery step below, requested early
+            const size_t ro = (size_t)yo * a.W;
+            unsigned pixw[GC];
+#pragma unroll
+            for (int j = 0; j < GC; ++j) {
+                const int x = s.xs + s.lane + 32 * j;
+                pixw[j] = (s.lane + 32 * j < s.outw && x < a.W) ? pix[ro + x] : 0u;
+            }
 #pragma unroll
             for (int j = 0; j < GC; ++j) { wA[s.lane + 32 * j] = va[j]; wB[s.lane + 32 * j] = vb[j]; }
             __syncwarp();
@@ -250,13 +268,13 @@ __global__ void __launch_bounds__(GNT) gf_recover_kernel(GuidedArgs a) {
                 for (int j = 0; j < GC; ++j) { wA[base + j] = ma[j]; wB[base + j] = mb[j]; }
             }
             __syncwarp();
-            const size_t ro = (size_t)yo * a.W;
-            for (int i = s.lane; i < s.outw; i += 32) {
+#pragma unroll
+            for (int jj = 0; jj < GC; ++jj) {
+                const int i = s.lane + 32 * jj;
                 const int x = s.xs + i;
-                if (x >= a.W) break;
-                const uint8_t* p = frame + (ro + x) * 3;
-                const int r0 = p[0], g0 = p[1], b0 = p[2];
-                double t = __dadd_rn(__dmul_rn(wA[i], sI[gray[ro + x]]), wB[i]);
+                if (i >= s.outw || x >= a.W) continue;
+                const int r0 = pixw[jj] & 255, g0 = (pixw[jj] >> 8) & 255, b0 = (pixw[jj] >> 16) & 255;
+                double t = __dadd_rn(__dmul_rn(wA[i], sI[pixw[jj] >> 24]), wB[i]);
                 t = t < 0.1 ? 0.1 : (t > 1.0 ? 1.0 : t);
                 // (img - A) in float32, / t and + A in float64, stored in the library's float type
                 double q0, q1, q2;
@@ -282,7 +300,9 @@ __global__ void __launch_bounds__(GNT) gf_recover_kernel(GuidedArgs a) {
                 atomicAdd(&shist[2 * kSelBinsA + sel_bin_a<T>(v2)], 1u);
             }
             __syncwarp();
-            row_sub(yo - s.lo);
+#pragma unroll
+            for (int j = 0; j < GC; ++j) { va[j] -= aL[j]; vb[j] -= bL[j]; }
+            if (yo + 1 < s.ye) row_load(yo + 1 - s.lo, aL, bL);
         }
     }
     __syncthreads();

@@ -85,7 +85,7 @@ struct GuidedArgs {
     int n_dehaze;                // number of dehaze strategies
     int dehaze_idx[kStrategiesMax];   // their strategy indices
     int rows_per_block;
-    uint8_t* gray_plane;         // [B][H][W]   gray byte of the (colour-corrected) frame
+    unsigned* pix_plane;         // [B][H][W]   R | G << 8 | B << 16 | gray << 24 of the (colour-corrected) frame
     float* dark_plane;           // [B][H][W]   min_c img / (A + guard)
     const uint8_t* frames;
     const CastTables* cast;

@@ -171,7 +171,7 @@ void plan_layout(uwie_engine* e) {
     L.ab = b.take(B * nd * 2 * N * 8);
     L.recovered = b.take(B * nd * N * 3 * tsz);
     L.targets = b.take(B * nd * kSelTargets * sizeof(SelTarget));
-    L.gf_gray = b.take(nd ? B * N : 0);
+    L.gf_gray = b.take(nd ? B * N * 4 : 0);
     L.gf_dark = b.take(nd ? B * N * 4 : 0);
     L.tile_lut = b.take(e->max_tiles ? B * S * kMaxTiles * 256 : 0);
     L.out = b.take(B * S * N * 3);
@@ -433,7 +433,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
             if (const char* ev = std::getenv("UWIE_GF_CHUNKS")) { const int v = std::atoi(ev); if (v >= 1 && v <= H) chunks = v; }
             ga.rows_per_block = (H + chunks - 1) / chunks;
         }
-        ga.gray_plane = e->at<uint8_t>(L.gf_gray); ga.dark_plane = e->at<float>(L.gf_dark);
+        ga.pix_plane = e->at<unsigned>(L.gf_gray); ga.dark_plane = e->at<float>(L.gf_dark);
         ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;
         ga.ab = e->at<double>(L.ab); ga.recovered = e->at<void>(L.recovered);
         ga.sel_hist_a = e->at<unsigned>(L.sel_hist_a);
