@@ -43,7 +43,8 @@ def _worker(rank, world, port, total, strategies, q):
     rec = shard.pack_records(scores, best, types, shard.shard_capacity(total, world))
     got = shard.gather_records(rec)
     s, b, t = shard.unpack_records(got, strategies)
-    q.put((rank, s, b, t))
+    # NumPy copies: tensors travel through the queue as shared-memory handles that die with the worker
+    q.put((rank, s.numpy().copy(), b.numpy().copy(), t.numpy().copy()))
     dist.destroy_process_group()
 
 
@@ -64,6 +65,7 @@ def test_gather_records_world2(total):
     want = idx[:, None, None] * 10 + torch.arange(strategies, dtype=torch.float64)[None, :, None] \
         + torch.arange(9, dtype=torch.float64)[None, None, :] / 10
     for _, s, b, t in results:
+        s, b, t = torch.from_numpy(s), torch.from_numpy(b), torch.from_numpy(t)
         assert torch.equal(s, want)                       # global image order, sentinels dropped
         assert torch.equal(b, (torch.arange(total) % strategies).to(torch.int32))
         assert torch.equal(t, (torch.arange(total) % 3).to(torch.int32))
