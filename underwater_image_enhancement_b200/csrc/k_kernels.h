@@ -11,6 +11,9 @@ namespace uwie {
 
 // ------------------------------------------------------------------ k_canny.cu
 enum { CANNY_QUADRANTS = 0, CANNY_PLANES = 1 };
+constexpr int kCannyTile = 64;       // tile side
+constexpr int kCannyListCap = 128;   // components of a tile that can touch its rim (<= 126: rim pixels of
+                                     // different components are never adjacent on the 252-pixel ring)
 struct CannyArgs {
     int mode;
     int H, W;
@@ -26,11 +29,13 @@ struct CannyArgs {
     const uint8_t* gray;        // [instances][H][W]
     int planes_per_img;
     // scratch + result
-    uint8_t* map;               // [planes][H][W]   0 / 1 weak / 2 strong
-    int* labels;                // [planes][H][W]
+    int* labels;                // [planes][H][W]   sparse: rim pixels of the tiles and roots of listed components
+    int2* tile_list;            // [tile slots][kCannyListCap]   {root pixel, size << 2 | strong | rim}
+    int* tile_n;                // [tile slots]
     unsigned* counts;           // QUADRANTS: [B][kQuadLevelsMax][4]; PLANES: [instances]
 };
 int launch_canny(const CannyArgs& a, int max_rows, int max_cols, int instances, cudaStream_t st);
+size_t canny_tile_slots(int max_rows, int max_cols, int instances);   // tile slots one launch uses
 
 // ------------------------------------------------------------------ k_stats.cu
 // per-channel 256-bin histograms of uint8 HWC frames: hist[B][3][256] (must be zeroed)

@@ -2,6 +2,7 @@
 // C ABI in include/uwie.h.  No CPU path: every entry point needs a CUDA device.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -42,7 +43,7 @@ struct Layout {
     size_t zero_begin, frame_hist, quad_hist, quad_counts, sel_hist_a, sel_hist_b, sel_hist_c, tab_keys,
         tab_counts, out_hist, qa,
         edge_counts, zero_end;
-    size_t recipes, ctab, status, types, cast, tables, rects, q_trace, light, map, labels, ab,
+    size_t recipes, ctab, status, types, cast, tables, rects, q_trace, light, tile_list, tile_n, labels, ab,
         recovered, targets, gf_gray, gf_dark, tile_lut, out, gray, cf_part, scores, best;
     size_t total;
 };
@@ -166,7 +167,13 @@ void plan_layout(uwie_engine* e) {
     L.rects = b.take(B * sizeof(QuadRect));
     L.q_trace = b.take(B * kQuadLevelsMax * 4 * 8);
     L.light = b.take(B * 3 * 4);
-    L.map = b.take(B * S * N);
+    {
+        size_t slots = canny_tile_slots(e->H, e->W, (int)(B * S));
+        if (nd && !e->quad_dims.empty())
+            slots = std::max(slots, canny_tile_slots(e->quad_dims[0].first, e->quad_dims[0].second, (int)(B * 4)));
+        L.tile_list = b.take(slots * kCannyListCap * sizeof(int2));
+        L.tile_n = b.take(slots * 4);
+    }
     L.labels = b.take(B * S * N * 4);
     L.ab = b.take(B * nd * 2 * N * 8);
     L.recovered = b.take(B * nd * N * 3 * tsz);
@@ -413,7 +420,8 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         ca.mode = CANNY_QUADRANTS; ca.H = H; ca.W = W; ca.low = 50; ca.high = 150;
         ca.frames = frames; ca.cast = sa.cast; ca.rects = qa.rects;
         ca.quad_hist = e->at<unsigned>(L.quad_hist);
-        ca.map = e->at<uint8_t>(L.map); ca.labels = e->at<int>(L.labels);
+        ca.labels = e->at<int>(L.labels);
+        ca.tile_list = e->at<int2>(L.tile_list); ca.tile_n = e->at<int>(L.tile_n);
         ca.counts = e->at<unsigned>(L.quad_counts);
         for (size_t lv = 0; lv < e->quad_dims.size(); ++lv) {
             ca.level = (int)lv;
@@ -483,7 +491,8 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     std::memset(&cq, 0, sizeof(cq));
     cq.mode = CANNY_PLANES; cq.H = H; cq.W = W; cq.low = 50; cq.high = 150;
     cq.gray = aa.gray; cq.planes_per_img = S;
-    cq.map = e->at<uint8_t>(L.map); cq.labels = e->at<int>(L.labels);
+    cq.labels = e->at<int>(L.labels);
+    cq.tile_list = e->at<int2>(L.tile_list); cq.tile_n = e->at<int>(L.tile_n);
     cq.counts = e->at<unsigned>(L.edge_counts);
     stage(e, st, "score_canny", launches);
     launches += launch_canny(cq, H, W, batch * S, st);
@@ -681,7 +690,6 @@ const void* uwie_engine_debug(const uwie_engine* e, const char* name, size_t* by
         {"edge_counts", L.edge_counts, B * S * 4},
         {"targets", L.targets, B * nd * kSelTargets * sizeof(SelTarget)},
         {"scores", L.scores, B * S * kScoreCols * 8},
-        {"map", L.map, B * S * N},
     };
     for (const Item& it : items) {
         if (std::strcmp(it.n, name) == 0) {
