@@ -7,17 +7,18 @@
 //
 // Only the COUNT is wanted, so no edge map and no per-pixel label plane is ever written:
 //   1. canny_tile_kernel   64x64 tile: gradient (column march over shared memory), NMS, double
-//                          threshold -> per-row candidate / strong bit masks; runs of candidates are
-//                          linked by a union-find in shared memory; every component gets
-//                          (size, holds-a-strong-pixel, touches-a-neighbouring-tile).  Components
-//                          that stay inside the tile are counted on the spot.  The others go to a
-//                          short per-tile list {root pixel, size, strong}, and the pixels on the
-//                          tile's rim get a label (root pixel index, -1 = not a candidate) in the
-//                          sparse label plane — about 6 % of the plane is touched.
-//   2. canny_merge_kernel  rim pixels link across tile borders (lock-free atomicMin union-find on
-//                          the root entries of the label plane).
-//   3. canny_list_kernel<false>  listed components that hold a strong pixel flag their global root.
-//   4. canny_list_kernel<true>   listed components whose global root is flagged add their size.
+//                          threshold -> per-row candidate / strong bit masks (64-bit words).  One warp
+//                          then floods the masks: E = candidates connected inside the tile to one of
+//                          its strong pixels (counted on the spot), P = other candidates that reach a
+//                          side shared with a neighbouring tile (pending).  Runs of P are linked by a
+//                          union-find in shared memory; each pending component goes to a short
+//                          per-tile list {root pixel, size}; the pixels on the tile's rim get a label
+//                          (edge / root pixel of a pending component / none) in the sparse label
+//                          plane — about 6 % of the plane is touched.
+//   2. canny_rim_kernel<false>  pending rim pixels link across tile borders (lock-free atomicMin
+//                          union-find on the root entries of the label plane).
+//   3. canny_rim_kernel<true>   a pending rim pixel next to a certain edge flags its global root.
+//   4. canny_list_kernel   listed components whose global root is flagged add their size.
 // A rectangle that fits one tile needs pass 1 only.
 #include "k_common.cuh"
 #include "k_kernels.h"
@@ -33,7 +34,7 @@ constexpr int MW = TW + 2, MH = TH + 2;           // magnitude tile with a 1-pix
 constexpr int SG_BYTES = (GH * GW + 15) & ~15;
 constexpr int LABEL_FLAG = 0x40000000;
 constexpr int LABEL_MASK = 0x3fffffff;
-constexpr int ATTR_STRONG = 1, ATTR_RIM = 2;      // component attribute word: size << 2 | flags
+constexpr int LAB_NONE = -1, LAB_EDGE = -2;       // rim labels that are not a pending component
 constexpr int RIM = 2 * TW + 2 * (TH - 2);
 
 static_assert(TW == 64, "a tile row is one 64-bit mask");
@@ -96,6 +97,35 @@ __device__ __forceinline__ int run_end(unsigned long long m, int x) {
     return holes ? __ffsll((long long)holes) - 1 : 64;
 }
 
+// all bits of the runs of `c` that hold a bit of `s` (s within c): the carry of c + s runs up through a
+// run from its lowest seed; the bit-reversed sum runs down
+__device__ __forceinline__ unsigned long long fill_runs(unsigned long long s, unsigned long long c) {
+    const unsigned long long up = (c ^ (c + s)) & c;
+    const unsigned long long rc = __brevll(c), rs = __brevll(s);
+    const unsigned long long dn = __brevll((rc ^ (rc + rs)) & rc);
+    return up | dn | s;
+}
+
+// 8-connected flood of the seeds (e0, e1) inside the candidates (c0, c1) of a 64-row tile held by one
+// warp, lane l owning rows 2l and 2l+1; seeds must lie inside the candidates.  Runs until nothing moves.
+__device__ __forceinline__ void flood_rows(unsigned long long& e0, unsigned long long& e1,
+                                           unsigned long long c0, unsigned long long c1, int lane) {
+    e0 = fill_runs(e0, c0); e1 = fill_runs(e1, c1);
+    while (true) {
+        unsigned long long up = __shfl_up_sync(0xffffffffu, e1, 1);
+        unsigned long long dn = __shfl_down_sync(0xffffffffu, e0, 1);
+        if (lane == 0) up = 0ull;
+        if (lane == 31) dn = 0ull;
+        unsigned long long n0 = up | e1;
+        n0 = (n0 | (n0 << 1) | (n0 >> 1)) & c0 & ~e0;
+        if (n0) e0 |= fill_runs(n0, c0);
+        unsigned long long n1 = dn | e0;
+        n1 = (n1 | (n1 << 1) | (n1 >> 1)) & c1 & ~e1;
+        if (n1) e1 |= fill_runs(n1, c1);
+        if (!__any_sync(0xffffffffu, (n0 | n1) != 0ull)) break;
+    }
+}
+
 // rim pixel k of a tile (row-major order is irrelevant): top row, bottom row, left and right columns
 __device__ __forceinline__ void rim_pixel(int k, int& ly, int& lx) {
     if (k < TW) { ly = 0; lx = k; }
@@ -115,16 +145,16 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     __shared__ __align__(16) unsigned char sraw[TH * TW * 4];
     __shared__ int slab[TH * TW];
     __shared__ unsigned long long smc[TH], sms[TH];    // per tile row: candidate / strong bit masks
+    __shared__ unsigned long long sme[TH], smp[TH];    // per tile row: certain edges / pending candidates
     __shared__ unsigned shist[MODE == CANNY_QUADRANTS ? 768 : 1];
-    __shared__ int s_nlist;
-    __shared__ unsigned s_cnt;
+    __shared__ int s_nlist, s_any;
     uint8_t (*sg)[GW] = reinterpret_cast<uint8_t (*)[GW]>(sraw);
     uint16_t (*sm)[MW] = reinterpret_cast<uint16_t (*)[MW]>(sraw + SG_BYTES);
     int* sattr = reinterpret_cast<int*>(sraw);
 
     const int tid = threadIdx.x;
     const size_t npix = (size_t)a.H * a.W;
-    if (tid == 0) { s_nlist = 0; s_cnt = 0; }
+    if (tid == 0) s_nlist = 0;
 
     // ---- gray with a 2-pixel replicated halo (replication at the RECTANGLE's border)
     if (MODE == CANNY_QUADRANTS) {
@@ -239,101 +269,110 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     }
     __syncthreads();      // sg / sm are dead from here on: sattr takes their place
 
-    // ---- link inside the tile.  A horizontal run of candidates is one node (its first pixel); runs of
+    // ---- hysteresis inside the tile: warp 0 floods the row masks (lane l owns rows 2l and 2l+1).
+    //   E = candidates connected, inside the tile, to one of its strong pixels: edges for certain
+    //   P = the other candidates that reach, inside the tile, a side shared with a neighbouring tile:
+    //       pending, they are edges iff a chain through other tiles ends at an edge
+    // Everything else is dropped here.  The other warps zero the attribute array meanwhile.
+    const bool has_top = ty0 > 0, has_bottom = ty0 + TH < rows, has_left = tx0 > 0, has_right = tx0 + TW < cols;
+    const bool any_nb = has_top || has_bottom || has_left || has_right;
+    if (tid < 32) {
+        const int r0 = 2 * tid, r1 = r0 + 1;
+        const unsigned long long c0 = smc[r0], c1 = smc[r1];
+        unsigned long long e0 = sms[r0], e1 = sms[r1];
+        flood_rows(e0, e1, c0, c1, tid);
+        unsigned cnt = (unsigned)(__popcll(e0) + __popcll(e1));
+        unsigned long long p0 = 0, p1 = 0;
+        if (any_nb) {                                                           // block-uniform
+            const unsigned long long side = (has_left ? 1ull : 0ull) | (has_right ? (1ull << 63) : 0ull);
+            const unsigned long long d0 = c0 & ~e0, d1 = c1 & ~e1;
+            p0 = d0 & ((r0 == 0 && has_top) ? ~0ull : side);
+            p1 = d1 & ((r1 == TH - 1 && has_bottom) ? ~0ull : side);
+            flood_rows(p0, p1, d0, d1, tid);
+        }
+        sme[r0] = e0; sme[r1] = e1; smp[r0] = p0; smp[r1] = p1;
+        cnt = warp_sum_u32(cnt);
+        if (tid == 0 && cnt) atomicAdd(&a.counts[j.out], cnt);
+        const int anyp = __any_sync(0xffffffffu, (p0 | p1) != 0ull);
+        if (tid == 0) s_any = anyp;
+    } else {
+        for (int i = tid - 32; i < TH * TW; i += NT - 32) sattr[i] = 0;
+    }
+    __syncthreads();
+
+    // ---- pending components: runs of P are the nodes of a union-find in shared memory; runs of
     // neighbouring rows are united once per contact: with U the row above,
     //   up set:            unite unless both W and NW are set (then the pixel to the left did it)
     //   up clear, NW set:  unite if W is clear          up clear, NE set:  unite if E is clear
-    for (int it = 0; it < TH * TW / NT; ++it) {
-        const int i = it * NT + tid;
-        const int ly = i >> 6, lx = i & 63;
-        const unsigned long long R = smc[ly];
-        sattr[i] = 0;
-        if (((R >> lx) & 1ull) && (lx == 0 || !((R >> (lx - 1)) & 1ull))) slab[i] = i;   // run starts are the nodes
-    }
-    __syncthreads();
-    for (int it = 0; it < TH * TW / NT; ++it) {
-        const int i = it * NT + tid;
-        const int ly = i >> 6, lx = i & 63;
-        if (ly == 0) continue;                                                  // warp-uniform
-        const unsigned long long R = smc[ly], U = smc[ly - 1];
-        if ((unsigned)(R >> (lx & 32)) == 0u || U == 0ull) continue;            // warp-uniform
-        if (!((R >> lx) & 1ull)) continue;
-        const bool up = (U >> lx) & 1ull;
-        const bool nw = lx > 0 && ((U >> (lx - 1)) & 1ull), ne = lx < TW - 1 && ((U >> (lx + 1)) & 1ull);
-        const bool w = lx > 0 && ((R >> (lx - 1)) & 1ull), e = lx < TW - 1 && ((R >> (lx + 1)) & 1ull);
-        if (up) {
-            if (!w || !nw) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + run_start(U, lx));
-        } else {
-            if (nw && !w) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + run_start(U, lx - 1));
-            if (ne && !e) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + lx + 1);   // NE starts its run (up is clear)
-        }
-    }
-    __syncthreads();
-
-    // ---- component attributes, gathered run by run (the thread of the run's first pixel)
-    const bool has_top = ty0 > 0, has_bottom = ty0 + TH < rows, has_left = tx0 > 0, has_right = tx0 + TW < cols;
-    const bool any_nb = has_top || has_bottom || has_left || has_right;
-    for (int it = 0; it < TH * TW / NT; ++it) {
-        const int i = it * NT + tid;
-        const int ly = i >> 6, lx = i & 63;
-        const unsigned long long R = smc[ly];
-        if ((unsigned)(R >> (lx & 32)) == 0u) continue;                         // warp-uniform
-        if (!((R >> lx) & 1ull) || (lx > 0 && ((R >> (lx - 1)) & 1ull))) continue;   // not a run start
-        const int end = run_end(R, lx);
-        const unsigned long long run = (end >= 64 ? ~0ull : ((1ull << end) - 1ull)) & (~0ull << lx);
-        int flags = (sms[ly] & run) ? ATTR_STRONG : 0;
-        if ((ly == 0 && has_top) || (ly == TH - 1 && has_bottom) || (lx == 0 && has_left) || (end == TW && has_right))
-            flags |= ATTR_RIM;
-        const int root = uf_find((volatile int*)slab, i);
-        atomicAdd(&sattr[root], (end - lx) << 2);
-        if (flags) atomicOr(&sattr[root], flags);
-    }
-    __syncthreads();
-
-    // ---- roots: count what is settled, list what touches a neighbouring tile
-    int* lab = a.labels + (size_t)j.plane * npix;
     const int slot = tile_slot();
-    unsigned cnt = 0;
-    for (int it = 0; it < TH * TW / NT; ++it) {
-        const int i = it * NT + tid;
-        const int ly = i >> 6, lx = i & 63;
-        const unsigned long long R = smc[ly];
-        if ((unsigned)(R >> (lx & 32)) == 0u) continue;
-        if (!((R >> lx) & 1ull) || (lx > 0 && ((R >> (lx - 1)) & 1ull))) continue;
-        if (slab[i] != i) continue;
-        const int attr = sattr[i];
-        if (attr & ATTR_RIM) {
+    int* lab = a.labels + (size_t)j.plane * npix;
+    if (s_any) {                                                                // block-uniform
+        for (int it = 0; it < TH * TW / NT; ++it) {
+            const int i = it * NT + tid;
+            const int ly = i >> 6, lx = i & 63;
+            const unsigned long long R = smp[ly];
+            if (((R >> lx) & 1ull) && (lx == 0 || !((R >> (lx - 1)) & 1ull))) slab[i] = i;   // run starts are the nodes
+        }
+        __syncthreads();
+        for (int it = 0; it < TH * TW / NT; ++it) {
+            const int i = it * NT + tid;
+            const int ly = i >> 6, lx = i & 63;
+            if (ly == 0) continue;                                                  // warp-uniform
+            const unsigned long long R = smp[ly], U = smp[ly - 1];
+            if ((unsigned)(R >> (lx & 32)) == 0u || U == 0ull) continue;            // warp-uniform
+            if (!((R >> lx) & 1ull)) continue;
+            const bool up = (U >> lx) & 1ull;
+            const bool nw = lx > 0 && ((U >> (lx - 1)) & 1ull), ne = lx < TW - 1 && ((U >> (lx + 1)) & 1ull);
+            const bool w = lx > 0 && ((R >> (lx - 1)) & 1ull), e = lx < TW - 1 && ((R >> (lx + 1)) & 1ull);
+            if (up) {
+                if (!w || !nw) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + run_start(U, lx));
+            } else {
+                if (nw && !w) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + run_start(U, lx - 1));
+                if (ne && !e) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + lx + 1);   // NE starts its run (up is clear)
+            }
+        }
+        __syncthreads();
+        // component sizes, gathered run by run (the thread of the run's first pixel)
+        for (int it = 0; it < TH * TW / NT; ++it) {
+            const int i = it * NT + tid;
+            const int ly = i >> 6, lx = i & 63;
+            const unsigned long long R = smp[ly];
+            if ((unsigned)(R >> (lx & 32)) == 0u) continue;                         // warp-uniform
+            if (!((R >> lx) & 1ull) || (lx > 0 && ((R >> (lx - 1)) & 1ull))) continue;   // not a run start
+            atomicAdd(&sattr[uf_find((volatile int*)slab, i)], run_end(R, lx) - lx);
+        }
+        __syncthreads();
+        // roots go to the tile's list and become nodes of the cross-tile union-find
+        for (int it = 0; it < TH * TW / NT; ++it) {
+            const int i = it * NT + tid;
+            const int ly = i >> 6, lx = i & 63;
+            const unsigned long long R = smp[ly];
+            if ((unsigned)(R >> (lx & 32)) == 0u) continue;
+            if (!((R >> lx) & 1ull) || (lx > 0 && ((R >> (lx - 1)) & 1ull))) continue;
+            if (slab[i] != i) continue;
             const int gp = (j.y0 + ty0 + ly) * a.W + (j.x0 + tx0 + lx);
             const int k = atomicAdd(&s_nlist, 1);
-            if (k < kCannyListCap) a.tile_list[(size_t)slot * kCannyListCap + k] = make_int2(gp, attr);
+            if (k < kCannyListCap) a.tile_list[(size_t)slot * kCannyListCap + k] = make_int2(gp, sattr[i]);
             lab[gp] = gp;
-        } else if (attr & ATTR_STRONG) {
-            cnt += (unsigned)(attr >> 2);
         }
     }
-    // ---- rim labels for the merge pass
+    // ---- rim labels for the cross-tile passes: LAB_EDGE, root pixel of a pending component, or LAB_NONE
     if (any_nb && tid < RIM) {
         int ly, lx;
         rim_pixel(tid, ly, lx);
         const int ry = ty0 + ly, rx = tx0 + lx;
         if (ry < rows && rx < cols) {
-            const unsigned long long R = smc[ly];
-            int v = -1;
+            const unsigned long long R = smp[ly];
+            int v = ((sme[ly] >> lx) & 1ull) ? LAB_EDGE : LAB_NONE;
             if ((R >> lx) & 1ull) {
                 const int root = uf_find((volatile int*)slab, ly * TW + run_start(R, lx));
                 v = (j.y0 + ty0 + (root >> 6)) * a.W + (j.x0 + tx0 + (root & 63));
             }
-            const int gp = (j.y0 + ry) * a.W + (j.x0 + rx);
-            lab[gp] = v;                   // (a root on the rim gets its own index, as above)
+            lab[(j.y0 + ry) * a.W + (j.x0 + rx)] = v;      // (a root on the rim gets its own index, as above)
         }
     }
-    cnt = warp_sum_u32(cnt);
-    if ((tid & 31) == 0 && cnt) atomicAdd(&s_cnt, cnt);
     __syncthreads();
-    if (tid == 0) {
-        a.tile_n[slot] = min(s_nlist, kCannyListCap);
-        if (s_cnt) atomicAdd(&a.counts[j.out], s_cnt);
-    }
+    if (tid == 0) a.tile_n[slot] = min(s_nlist, kCannyListCap);
 
     if (MODE == CANNY_QUADRANTS) {
         unsigned* gh = a.quad_hist + (size_t)j.out * 768;
@@ -344,9 +383,29 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     }
 }
 
-// ---- pass 2: links that cross a tile border.  One thread per rim pixel; every cross-tile pair of
-// 8-neighbours is handled by its lower / right member (neighbours W, NW, N, NE).
-__global__ void __launch_bounds__(NT) canny_merge_kernel(CannyArgs a) {
+// ---- pass 2 / 3 walk the rims.  One thread per rim pixel; every cross-tile pair of 8-neighbours is
+// handled by its lower / right member (neighbours W, NW, N, NE).
+//   FLAG = false: two pending pixels -> their components are united (lock-free atomicMin union-find
+//                 on the root entries of the label plane)
+//   FLAG = true : a pending pixel next to a certain edge -> its global root is flagged
+template <bool FLAG>
+__device__ __forceinline__ void rim_pair(int* lab, int p, int lp, int q) {
+    const int lq = lab[q];
+    if (!FLAG) {
+        if (lp >= 0 && lq >= 0) uf_union(lab, p, q);
+    } else {
+        int t = -1;
+        if (lp >= 0 && lq == LAB_EDGE) t = p;
+        else if (lp == LAB_EDGE && lq >= 0) t = q;
+        if (t >= 0) {
+            const int root = uf_find((volatile int*)lab, t);
+            if (!(lab[root] & LABEL_FLAG)) atomicOr(&lab[root], LABEL_FLAG);
+        }
+    }
+}
+
+template <bool FLAG>
+__global__ void __launch_bounds__(NT) canny_rim_kernel(CannyArgs a) {
     const Job j = make_job(a, blockIdx.z);
     const int rows = j.y1 - j.y0, cols = j.x1 - j.x0;
     const int ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
@@ -358,18 +417,18 @@ __global__ void __launch_bounds__(NT) canny_merge_kernel(CannyArgs a) {
     const int ry = ty0 + ly, rx = tx0 + lx;
     if (ry >= rows || rx >= cols) return;
     const int p = (j.y0 + ry) * a.W + (j.x0 + rx);
-    if (lab[p] < 0) return;
-    if (lx == 0 && rx > 0 && lab[p - 1] >= 0) uf_union(lab, p, p - 1);
+    const int lp = lab[p];
+    if (lp == LAB_NONE) return;
+    if (lx == 0 && rx > 0) rim_pair<FLAG>(lab, p, lp, p - 1);
     if (ry > 0) {
         const int up = p - a.W;
-        if ((lx == 0 || ly == 0) && rx > 0 && lab[up - 1] >= 0) uf_union(lab, p, up - 1);
-        if (ly == 0 && lab[up] >= 0) uf_union(lab, p, up);
-        if ((ly == 0 || lx == TW - 1) && rx + 1 < cols && lab[up + 1] >= 0) uf_union(lab, p, up + 1);
+        if ((lx == 0 || ly == 0) && rx > 0) rim_pair<FLAG>(lab, p, lp, up - 1);
+        if (ly == 0) rim_pair<FLAG>(lab, p, lp, up);
+        if ((ly == 0 || lx == TW - 1) && rx + 1 < cols) rim_pair<FLAG>(lab, p, lp, up + 1);
     }
 }
 
-// ---- pass 3 / 4 walk the per-tile lists
-template <bool COUNT>
+// ---- pass 4: listed (pending) components whose global root is flagged add their size
 __global__ void __launch_bounds__(kCannyListCap) canny_list_kernel(CannyArgs a) {
     const Job j = make_job(a, blockIdx.z);
     const int rows = j.y1 - j.y0, cols = j.x1 - j.x0;
@@ -377,29 +436,22 @@ __global__ void __launch_bounds__(kCannyListCap) canny_list_kernel(CannyArgs a) 
     if (ty0 >= rows || tx0 >= cols) return;
     const int slot = tile_slot();
     const int n = a.tile_n[slot];
+    if (n == 0) return;                                       // block-uniform
     int* lab = a.labels + (size_t)j.plane * ((size_t)a.H * a.W);
     unsigned cnt = 0;
     if ((int)threadIdx.x < n) {
         const int2 e = a.tile_list[(size_t)slot * kCannyListCap + threadIdx.x];
-        if (COUNT) {
-            const int root = uf_find((volatile int*)lab, e.x);
-            if (lab[root] & LABEL_FLAG) cnt = (unsigned)(e.y >> 2);
-        } else if (e.y & ATTR_STRONG) {
-            const int root = uf_find((volatile int*)lab, e.x);
-            if (!(lab[root] & LABEL_FLAG)) atomicOr(&lab[root], LABEL_FLAG);
-        }
+        const int root = uf_find((volatile int*)lab, e.x);
+        if (lab[root] & LABEL_FLAG) cnt = (unsigned)e.y;
     }
-    if (COUNT) {
-        if (n == 0) return;                                   // block-uniform
-        cnt = warp_sum_u32(cnt);
-        __shared__ unsigned sw[kCannyListCap / 32];
-        if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = cnt;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned t = 0;
-            for (int w = 0; w < kCannyListCap / 32; ++w) t += sw[w];
-            if (t) atomicAdd(&a.counts[j.out], t);
-        }
+    cnt = warp_sum_u32(cnt);
+    __shared__ unsigned sw[kCannyListCap / 32];
+    if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = 0;
+        for (int w = 0; w < kCannyListCap / 32; ++w) t += sw[w];
+        if (t) atomicAdd(&a.counts[j.out], t);
     }
 }
 
@@ -416,9 +468,9 @@ int launch_canny(const CannyArgs& a, int max_rows, int max_cols, int instances, 
     if (a.mode == CANNY_QUADRANTS) canny_tile_kernel<CANNY_QUADRANTS><<<grid, NT, 0, st>>>(a);
     else canny_tile_kernel<CANNY_PLANES><<<grid, NT, 0, st>>>(a);
     if (grid.x == 1 && grid.y == 1) return 1;
-    canny_merge_kernel<<<grid, NT, 0, st>>>(a);
-    canny_list_kernel<false><<<grid, kCannyListCap, 0, st>>>(a);
-    canny_list_kernel<true><<<grid, kCannyListCap, 0, st>>>(a);
+    canny_rim_kernel<false><<<grid, NT, 0, st>>>(a);
+    canny_rim_kernel<true><<<grid, NT, 0, st>>>(a);
+    canny_list_kernel<<<grid, kCannyListCap, 0, st>>>(a);
     return 4;
 }
 
