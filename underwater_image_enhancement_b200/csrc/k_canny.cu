@@ -256,7 +256,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         bool cand = false;
         if (m > a.low) {
             const int dir = v >> 12;
-            const int d = dir == 0 ? 1 : (dir == 1 ? MW : (dir == 2 ? MW - 1 : MW + 1));
+            const int d = (int)((((unsigned)(MW + 1) << 24) | ((MW - 1) << 16) | (MW << 8) | 1u) >> (dir * 8)) & 0xff;
             const int mf = c[-d] & 0xfff, ms = c[d] & 0xfff;
             cand = m > mf && m > ms - (dir < 2 ? 1 : 0);
         }
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     //   E = candidates connected, inside the tile, to one of its strong pixels: edges for certain
     //   P = the other candidates that reach, inside the tile, a side shared with a neighbouring tile:
     //       pending, they are edges iff a chain through other tiles ends at an edge
-    // Everything else is dropped here.  The other warps zero the attribute array meanwhile.
+    // Everything else is dropped here.
     const bool has_top = ty0 > 0, has_bottom = ty0 + TH < rows, has_left = tx0 > 0, has_right = tx0 + TW < cols;
     const bool any_nb = has_top || has_bottom || has_left || has_right;
     if (tid < 32) {
@@ -295,62 +295,50 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         if (tid == 0 && cnt) atomicAdd(&a.counts[j.out], cnt);
         const int anyp = __any_sync(0xffffffffu, (p0 | p1) != 0ull);
         if (tid == 0) s_any = anyp;
-    } else {
-        for (int i = tid - 32; i < TH * TW; i += NT - 32) sattr[i] = 0;
     }
     __syncthreads();
 
-    // ---- pending components: runs of P are the nodes of a union-find in shared memory; runs of
-    // neighbouring rows are united once per contact: with U the row above,
-    //   up set:            unite unless both W and NW are set (then the pixel to the left did it)
-    //   up clear, NW set:  unite if W is clear          up clear, NE set:  unite if E is clear
+    // ---- pending components: runs of P are the nodes of a union-find in shared memory (labels in
+    // slab, sizes in sattr, both indexed by the run's first pixel)
     const int slot = tile_slot();
     int* lab = a.labels + (size_t)j.plane * npix;
     if (s_any) {                                                                // block-uniform
-        for (int it = 0; it < TH * TW / NT; ++it) {
-            const int i = it * NT + tid;
-            const int ly = i >> 6, lx = i & 63;
-            const unsigned long long R = smp[ly];
-            if (((R >> lx) & 1ull) && (lx == 0 || !((R >> (lx - 1)) & 1ull))) slab[i] = i;   // run starts are the nodes
+        // P is sparse: one thread per tile row walks the runs of its 64-bit mask
+        const bool rowt = tid < TH;
+        const unsigned long long R = rowt ? smp[tid] : 0ull;
+        const unsigned long long U = (rowt && tid > 0) ? smp[tid - 1] : 0ull;
+        for (unsigned long long m = R; m;) {                                    // nodes = first pixels of the runs
+            const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
+            slab[tid * TW + s0] = tid * TW + s0; sattr[tid * TW + s0] = 0;
+            m &= e0 >= 64 ? 0ull : (~0ull << e0);
         }
         __syncthreads();
-        for (int it = 0; it < TH * TW / NT; ++it) {
-            const int i = it * NT + tid;
-            const int ly = i >> 6, lx = i & 63;
-            if (ly == 0) continue;                                                  // warp-uniform
-            const unsigned long long R = smp[ly], U = smp[ly - 1];
-            if ((unsigned)(R >> (lx & 32)) == 0u || U == 0ull) continue;            // warp-uniform
-            if (!((R >> lx) & 1ull)) continue;
-            const bool up = (U >> lx) & 1ull;
-            const bool nw = lx > 0 && ((U >> (lx - 1)) & 1ull), ne = lx < TW - 1 && ((U >> (lx + 1)) & 1ull);
-            const bool w = lx > 0 && ((R >> (lx - 1)) & 1ull), e = lx < TW - 1 && ((R >> (lx + 1)) & 1ull);
-            if (up) {
-                if (!w || !nw) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + run_start(U, lx));
-            } else {
-                if (nw && !w) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + run_start(U, lx - 1));
-                if (ne && !e) uf_union(slab, ly * TW + run_start(R, lx), (ly - 1) * TW + lx + 1);   // NE starts its run (up is clear)
+        for (unsigned long long m = R; m;) {                                    // link to the runs of the row above
+            const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
+            m &= e0 >= 64 ? 0ull : (~0ull << e0);
+            // 8-connectivity: columns s0-1 .. e0 of the row above
+            const unsigned long long hi = e0 >= 63 ? ~0ull : ((1ull << (e0 + 1)) - 1ull);
+            const unsigned long long lo = s0 == 0 ? ~0ull : (~0ull << (s0 - 1));
+            for (unsigned long long t = U & hi & lo; t;) {
+                const int b0 = __ffsll((long long)t) - 1;
+                const int ue = run_end(U, b0);
+                uf_union(slab, tid * TW + s0, (tid - 1) * TW + run_start(U, b0));
+                t &= ue >= 64 ? 0ull : (~0ull << ue);
             }
         }
         __syncthreads();
-        // component sizes, gathered run by run (the thread of the run's first pixel)
-        for (int it = 0; it < TH * TW / NT; ++it) {
-            const int i = it * NT + tid;
-            const int ly = i >> 6, lx = i & 63;
-            const unsigned long long R = smp[ly];
-            if ((unsigned)(R >> (lx & 32)) == 0u) continue;                         // warp-uniform
-            if (!((R >> lx) & 1ull) || (lx > 0 && ((R >> (lx - 1)) & 1ull))) continue;   // not a run start
-            atomicAdd(&sattr[uf_find((volatile int*)slab, i)], run_end(R, lx) - lx);
+        for (unsigned long long m = R; m;) {                                    // component sizes
+            const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
+            m &= e0 >= 64 ? 0ull : (~0ull << e0);
+            atomicAdd(&sattr[uf_find((volatile int*)slab, tid * TW + s0)], e0 - s0);
         }
         __syncthreads();
-        // roots go to the tile's list and become nodes of the cross-tile union-find
-        for (int it = 0; it < TH * TW / NT; ++it) {
-            const int i = it * NT + tid;
-            const int ly = i >> 6, lx = i & 63;
-            const unsigned long long R = smp[ly];
-            if ((unsigned)(R >> (lx & 32)) == 0u) continue;
-            if (!((R >> lx) & 1ull) || (lx > 0 && ((R >> (lx - 1)) & 1ull))) continue;
+        for (unsigned long long m = R; m;) {                                    // roots -> list, nodes of the cross-tile union-find
+            const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
+            m &= e0 >= 64 ? 0ull : (~0ull << e0);
+            const int i = tid * TW + s0;
             if (slab[i] != i) continue;
-            const int gp = (j.y0 + ty0 + ly) * a.W + (j.x0 + tx0 + lx);
+            const int gp = (j.y0 + ty0 + tid) * a.W + (j.x0 + tx0 + s0);
             const int k = atomicAdd(&s_nlist, 1);
             if (k < kCannyListCap) a.tile_list[(size_t)slot * kCannyListCap + k] = make_int2(gp, sattr[i]);
             lab[gp] = gp;
