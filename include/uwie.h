@@ -132,6 +132,38 @@ int uwie_engine_profile_read(uwie_engine* e, char* names, double* ms, int* kerne
  *  "tile_lut", "out_hist", "gray", "qa", "edge_counts", "targets").  NULL if unknown. */
 const void* uwie_engine_debug(const uwie_engine* e, const char* name, size_t* bytes);
 
+/* ---------------------------------------------------------------------------------------------
+ * VGG-guided path (use_trained_model.py): the per-pixel pieces around the network, which itself
+ * stays on PyTorch.  Stateless calls on caller-owned device memory; `workspace_dev` must hold
+ * uwie_vgg_workspace_bytes(batch) bytes; all are asynchronous on `stream`.
+ * ------------------------------------------------------------------------------------------- */
+#define UWIE_VGG_FEATURES 79      /* vgg_16_UIE.py:462-466: 18 statistics zero-padded to 79 */
+
+size_t uwie_vgg_workspace_bytes(int batch);
+
+/* DifferentiableEnhancement.forward (vgg_16_UIE.py:32-55): colour stretch between the order
+ * statistics sorted[int(L/100 * n)] of each plane (VGG:57-92), dark-channel dehaze with A = 0.6
+ * (VGG:94-117) when `omega` is given, pow(x + 1e-8, gamma) (VGG:119-128) when `gamma` is given,
+ * clamp.  img / out: float32 NCHW [batch][3][H][W] on the device; l_low, l_high, omega, gamma:
+ * HOST arrays of `batch` floats (omega and gamma may be NULL = step skipped, like a missing key). */
+int uwie_vgg_enhance(const float* img_dev, int batch, int height, int width,
+                     const float* l_low, const float* l_high, const float* omega, const float* gamma,
+                     float* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* extract_all_features (vgg_16_UIE.py:435-466) of uint8 RGB frames [batch][H][W][3] (the reference
+ * divides by 255 first, VGG:425-433): per channel mean, std, min, max, median; overall mean, std,
+ * mean of squares; zeros up to 79.  feat_dev: float32 [batch][79]. */
+int uwie_vgg_features_u8(const uint8_t* frames_dev, int batch, int height, int width, float* feat_dev,
+                         void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* EnhancementPredictor._preprocess_for_vgg (use_trained_model.py:39-46): truncate to bytes,
+ * cv2.resize(size x size, INTER_LINEAR) in 8-bit fixed point, / 255, ImageNet normalisation,
+ * HWC -> CHW.  Input uint8 or float32 [0,1] HWC frames; out_dev: float32 [batch][3][size][size]. */
+int uwie_vgg_preprocess_u8(const uint8_t* frames_dev, int batch, int height, int width, int size,
+                           float* out_dev, void* stream);
+int uwie_vgg_preprocess_f32(const float* img_dev, int batch, int height, int width, int size,
+                            float* out_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -431,3 +431,70 @@ def np_percentile_plan(n: int, q, f32: bool):
     if float(vi) >= n - 1:
         return n - 1, type(vi)(0)
     return int(k), vi - type(vi)(k)
+
+
+# ----------------------------------------------------------------------------------------
+# VGG-guided path: the per-pixel pieces around the network
+#   VGG = vgg_16_UIE.py, UTM = use_trained_model.py
+# ----------------------------------------------------------------------------------------
+
+
+def vgg_stretch_rank(level: float, n: int) -> int:
+    """int((L / 100.0) * n) clamped to [0, n - 1]  (VGG:78-82; L is a float32 tensor item)."""
+    k = int((float(np.float32(level)) / 100.0) * n)
+    return max(0, min(k, n - 1))
+
+
+def vgg_enhance(img: np.ndarray, l_low, l_high, omega=None, gamma=None) -> np.ndarray:
+    """DifferentiableEnhancement.forward on a float32 NCHW batch (VGG:32-55), all steps in float32."""
+    img = np.asarray(img, dtype=np.float32)
+    B, C, H, W = img.shape
+    n = H * W
+    out = np.zeros_like(img)
+    for b in range(B):
+        for c in range(C):                                           # VGG:70-90
+            plane = img[b, c]
+            srt = np.sort(plane.reshape(-1))
+            p_lo = srt[vgg_stretch_rank(l_low[b], n)]
+            p_hi = srt[vgg_stretch_rank(l_high[b], n)]
+            rng = np.float32(np.float32(p_hi - p_lo) + np.float32(1e-8))
+            out[b, c] = np.clip((plane - p_lo) / rng, 0, 1)
+    if omega is not None:                                            # VGG:94-117
+        w = np.asarray(omega, dtype=np.float32).reshape(-1, 1, 1, 1)
+        dark = out.min(axis=1, keepdims=True)
+        t = np.clip(np.float32(1) - w * dark, np.float32(0.1), np.float32(1.0))
+        out = np.clip((out - np.float32(0.6)) / t + np.float32(0.6), 0, 1).astype(np.float32)
+    if gamma is not None:                                            # VGG:119-128
+        g = np.asarray(gamma, dtype=np.float32).reshape(-1, 1, 1, 1)
+        out = np.power(out + np.float32(1e-8), g).astype(np.float32)
+    return np.clip(out, 0, 1).astype(np.float32)                     # VGG:55
+
+
+def vgg_features(img: np.ndarray) -> np.ndarray:
+    """extract_all_features (VGG:435-466): 18 statistics, zero-padded to 79, float32."""
+    img = np.asarray(img)
+    if img.dtype == np.uint8:                                        # VGG:425-433
+        img = img.astype(np.float32) / 255.0
+    else:
+        img = img.astype(np.float32)
+        if img.max() > 1.0:
+            img = img / 255.0
+    feats = []
+    for c in range(3):
+        ch = img[:, :, c]
+        feats += [float(np.mean(ch)), float(np.std(ch)), float(np.min(ch)), float(np.max(ch)),
+                  float(np.median(ch))]
+    feats += [float(np.mean(img)), float(np.std(img)), float(np.mean(img ** 2))]
+    feats += [0.0] * (79 - len(feats))
+    return np.array(feats[:79], dtype=np.float32)
+
+
+def vgg_preprocess(img: np.ndarray, size: int = 224) -> np.ndarray:
+    """_preprocess_for_vgg (UTM:39-46): 8-bit bilinear resize, /255, ImageNet normalisation, CHW."""
+    if img.dtype != np.uint8:
+        img = (img * 255).astype(np.uint8)
+    small = cv2.resize(img, (size, size), interpolation=cv2.INTER_LINEAR).astype(np.float32) / 255.0
+    chw = np.ascontiguousarray(small.transpose(2, 0, 1))
+    mean = np.array([0.485, 0.456, 0.406], np.float32).reshape(3, 1, 1)
+    std = np.array([0.229, 0.224, 0.225], np.float32).reshape(3, 1, 1)
+    return ((chw - mean) / std).astype(np.float32)

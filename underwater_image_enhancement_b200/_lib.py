@@ -17,7 +17,9 @@ OK, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_SELECT = 0, -1, -2, -3, -4
 EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_bytes", "uwie_engine_create",
            "uwie_engine_destroy", "uwie_enhance_score", "uwie_enhance_score_host", "uwie_engine_check",
            "uwie_engine_last_launches", "uwie_engine_debug", "uwie_engine_profile",
-           "uwie_engine_profile_read")
+           "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_features_u8",
+           "uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32")
+VGG_FEATURES = 79
 STAGE_NAME_LEN = 32
 
 
@@ -80,6 +82,19 @@ def load() -> C.CDLL:
     lib.uwie_engine_profile_read.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_int),
                                              C.POINTER(C.c_int), C.c_int]
     lib.uwie_engine_profile_read.restype = C.c_int
+    lib.uwie_vgg_workspace_bytes.argtypes = [C.c_int]
+    lib.uwie_vgg_workspace_bytes.restype = C.c_size_t
+    fp = C.POINTER(C.c_float)
+    lib.uwie_vgg_enhance.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, fp, fp, fp, fp, C.c_void_p, C.c_void_p,
+                                     C.c_size_t, C.c_void_p]
+    lib.uwie_vgg_enhance.restype = C.c_int
+    lib.uwie_vgg_features_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
+                                         C.c_void_p]
+    lib.uwie_vgg_features_u8.restype = C.c_int
+    for name in ("uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32"):
+        fn = getattr(lib, name)
+        fn.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        fn.restype = C.c_int
     _lib = lib
     return lib
 

@@ -1,0 +1,434 @@
+// The pieces of the VGG-guided path that are per-pixel work; the network itself
+// stays on PyTorch.
+//   DifferentiableEnhancement.forward / color_stretch_batch / dehaze_batch / gamma_correction
+//                                      vgg_16_UIE.py:32-128
+//   extract_all_features (18 statistics zero-padded to 79)         vgg_16_UIE.py:435-466
+//   EnhancementPredictor._preprocess_for_vgg (8-bit bilinear resize + ImageNet normalisation)
+//                                      use_trained_model.py:39-46
+// C ABI: include/uwie.h (uwie_vgg_*).  Stateless: the caller owns the workspace.
+//
+// color_stretch_batch takes sorted[int(L/100 * n)] of every (image, channel) plane: an exact order
+// statistic, found here by a three-pass most-significant-digit radix selection on the sortable
+// bit pattern of the float32 values (11 / 11 / 10 bits, shared-memory histograms) instead of a sort.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/uwie.h"
+#include "k_common.cuh"
+#include "k_kernels.h"
+
+namespace uwie {
+int uwie_fail(int code, const std::string& msg);   // uwie_engine.cu
+}
+using namespace uwie;
+
+namespace {
+
+constexpr int NT = 256;
+constexpr int kBinsAB = 2048, kBinsC = 1024;
+constexpr int kTargets = 2;                 // low / high order statistic of a plane
+constexpr int kFeat = 79;                   // vgg_16_UIE.py:462-466 pads to 79
+
+struct SelState {                           // per (plane, target)
+    long long rank;                         // rank still to resolve inside the current prefix
+    unsigned prefix;                        // key bits resolved so far
+    float value;                            // the order statistic, once all 32 bits are known
+};
+
+// monotone map float32 -> uint32 (negative values below positive ones, -0 < +0)
+__device__ __forceinline__ unsigned sort_key(float x) {
+    const unsigned u = __float_as_uint(x);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_value(unsigned k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// PASS 0: histogram of key >> 21 (shared by both targets)
+// PASS 1: per target, keys with key >> 21 == prefix: histogram of (key >> 10) & 2047
+// PASS 2: per target, keys with key >> 10 == prefix: histogram of key & 1023
+template <int PASS>
+__global__ void __launch_bounds__(NT) vgg_sel_hist_kernel(const float* __restrict__ data, long long n, long long plane_stride,
+                                                          int elem_stride, const SelState* __restrict__ state,
+                                                          unsigned* __restrict__ hist) {
+    constexpr int BINS = PASS == 2 ? kBinsC : kBinsAB;
+    constexpr int NH = PASS == 0 ? 1 : kTargets;
+    __shared__ unsigned sh[NH][BINS];
+    const int plane = blockIdx.y;
+    for (int i = threadIdx.x; i < NH * BINS; i += NT) (&sh[0][0])[i] = 0;
+    unsigned pre[kTargets] = {0, 0};
+    if (PASS > 0) {
+#pragma unroll
+        for (int t = 0; t < kTargets; ++t) pre[t] = state[plane * kTargets + t].prefix;
+    }
+    __syncthreads();
+    const float* p = data + (size_t)plane * plane_stride;
+    auto visit = [&](float x) {
+        const unsigned k = sort_key(x);
+        if (PASS == 0) atomicAdd(&sh[0][k >> 21], 1u);
+        else if (PASS == 1) {
+#pragma unroll
+            for (int t = 0; t < kTargets; ++t) if ((k >> 21) == pre[t]) atomicAdd(&sh[t][(k >> 10) & 2047u], 1u);
+        } else {
+#pragma unroll
+            for (int t = 0; t < kTargets; ++t) if ((k >> 10) == pre[t]) atomicAdd(&sh[t][k & 1023u], 1u);
+        }
+    };
+    if (elem_stride == 1 && (n & 3) == 0 && (plane_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(data) & 15) == 0) {
+        const float4* q = reinterpret_cast<const float4*>(p);
+        for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < n / 4; i += (long long)gridDim.x * NT) {
+            const float4 v = __ldg(q + i);
+            visit(v.x); visit(v.y); visit(v.z); visit(v.w);
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < n; i += (long long)gridDim.x * NT)
+            visit(p[i * elem_stride]);
+    }
+    __syncthreads();
+    unsigned* gh = hist + (size_t)plane * NH * BINS;
+    for (int i = threadIdx.x; i < NH * BINS; i += NT) {
+        const unsigned v = (&sh[0][0])[i];
+        if (v) atomicAdd(&gh[i], v);
+    }
+}
+
+// one block per plane: walk the histogram of each target to the bin holding its rank
+template <int PASS>
+__global__ void __launch_bounds__(NT) vgg_sel_scan_kernel(SelState* state, unsigned* hist) {
+    constexpr int BINS = PASS == 2 ? kBinsC : kBinsAB;
+    constexpr int NH = PASS == 0 ? 1 : kTargets;
+    constexpr int PER = BINS / NT;
+    const int plane = blockIdx.x;
+    __shared__ unsigned long long part[NT];
+    for (int t = 0; t < kTargets; ++t) {
+        unsigned* h = hist + ((size_t)plane * NH + (PASS == 0 ? 0 : t)) * BINS;
+        unsigned long long s = 0;
+        for (int i = 0; i < PER; ++i) s += h[threadIdx.x * PER + i];
+        part[threadIdx.x] = s;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            SelState st = state[plane * kTargets + t];
+            unsigned long long acc = 0;
+            int seg = 0;
+            while (seg < NT - 1 && acc + part[seg] <= (unsigned long long)st.rank) acc += part[seg++];
+            int bin = seg * PER;
+            while (bin < seg * PER + PER - 1 && acc + h[bin] <= (unsigned long long)st.rank) acc += h[bin++];
+            st.rank -= (long long)acc;
+            st.prefix = PASS == 0 ? (unsigned)bin : ((st.prefix << (PASS == 1 ? 11 : 10)) | (unsigned)bin);
+            if (PASS == 2) st.value = key_value(st.prefix);
+            state[plane * kTargets + t] = st;
+        }
+        __syncthreads();
+    }
+    // leave the histograms clean for the next pass / call
+    for (int i = threadIdx.x; i < NH * BINS; i += NT) hist[(size_t)plane * NH * BINS + i] = 0;
+}
+
+struct EnhanceParams {       // per image, device copy
+    float omega, gamma;
+};
+
+__device__ __forceinline__ float clamp01(float x) { return fminf(fmaxf(x, 0.f), 1.f); }
+
+// stretch -> dehaze -> gamma -> clamp on one pixel; every step rounds to float32 like the tensor ops
+__device__ __forceinline__ void enhance_pixel(float& r, float& g, float& b, const float* lo, const float* rng,
+                                              bool dehaze, float omega, bool gamma_on, float gamma) {
+    r = clamp01(__fdiv_rn(__fsub_rn(r, lo[0]), rng[0]));        // VGG:88-90
+    g = clamp01(__fdiv_rn(__fsub_rn(g, lo[1]), rng[1]));
+    b = clamp01(__fdiv_rn(__fsub_rn(b, lo[2]), rng[2]));
+    if (dehaze) {                                              // VGG:94-117, A = 0.6
+        const float d = fminf(fminf(r, g), b);
+        float t = __fsub_rn(1.0f, __fmul_rn(omega, d));
+        t = fminf(fmaxf(t, 0.1f), 1.0f);
+        r = clamp01(__fadd_rn(__fdiv_rn(__fsub_rn(r, 0.6f), t), 0.6f));
+        g = clamp01(__fadd_rn(__fdiv_rn(__fsub_rn(g, 0.6f), t), 0.6f));
+        b = clamp01(__fadd_rn(__fdiv_rn(__fsub_rn(b, 0.6f), t), 0.6f));
+    }
+    if (gamma_on) {                                            // VGG:119-128
+        r = powf(__fadd_rn(r, 1e-8f), gamma);
+        g = powf(__fadd_rn(g, 1e-8f), gamma);
+        b = powf(__fadd_rn(b, 1e-8f), gamma);
+    }
+    r = clamp01(r); g = clamp01(g); b = clamp01(b);            // VGG:55
+}
+
+__global__ void __launch_bounds__(NT) vgg_enhance_kernel(const float* __restrict__ img, float* __restrict__ out, long long n,
+                                                         const SelState* __restrict__ state,
+                                                         const EnhanceParams* __restrict__ prm, int dehaze, int gamma_on) {
+    const int b = blockIdx.y;
+    __shared__ float lo[3], rng[3];
+    if (threadIdx.x < 3) {
+        const float p_lo = state[(b * 3 + threadIdx.x) * kTargets + 0].value;
+        const float p_hi = state[(b * 3 + threadIdx.x) * kTargets + 1].value;
+        lo[threadIdx.x] = p_lo;
+        rng[threadIdx.x] = __fadd_rn(__fsub_rn(p_hi, p_lo), 1e-8f);     // VGG:87
+    }
+    __syncthreads();
+    const float omega = prm[b].omega, gamma = prm[b].gamma;
+    const float* p = img + (size_t)b * 3 * n;
+    float* o = out + (size_t)b * 3 * n;
+    if ((n & 3) == 0 && ((reinterpret_cast<uintptr_t>(img) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        const float4* pr = reinterpret_cast<const float4*>(p);
+        const float4* pg = reinterpret_cast<const float4*>(p + n);
+        const float4* pb = reinterpret_cast<const float4*>(p + 2 * n);
+        float4* qr = reinterpret_cast<float4*>(o);
+        float4* qg = reinterpret_cast<float4*>(o + n);
+        float4* qb = reinterpret_cast<float4*>(o + 2 * n);
+        for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < n / 4; i += (long long)gridDim.x * NT) {
+            float4 r = __ldg(pr + i), g = __ldg(pg + i), bl = __ldg(pb + i);
+            enhance_pixel(r.x, g.x, bl.x, lo, rng, dehaze, omega, gamma_on, gamma);
+            enhance_pixel(r.y, g.y, bl.y, lo, rng, dehaze, omega, gamma_on, gamma);
+            enhance_pixel(r.z, g.z, bl.z, lo, rng, dehaze, omega, gamma_on, gamma);
+            enhance_pixel(r.w, g.w, bl.w, lo, rng, dehaze, omega, gamma_on, gamma);
+            qr[i] = r; qg[i] = g; qb[i] = bl;
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < n; i += (long long)gridDim.x * NT) {
+            float r = p[i], g = p[n + i], bl = p[2 * n + i];
+            enhance_pixel(r, g, bl, lo, rng, dehaze, omega, gamma_on, gamma);
+            o[i] = r; o[n + i] = g; o[2 * n + i] = bl;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- 18 statistics from the byte histograms
+// img = frame / 255 in float32 (vgg_16_UIE.py:425-433); all statistics are functions of the three
+// 256-bin histograms.  Sums are taken in float64 and rounded once (NumPy sums float32 pairwise; the
+// difference is below 1e-6 relative, inside the 1e-4 tolerance of the float stages).
+__global__ void __launch_bounds__(256) vgg_features_kernel(const unsigned* __restrict__ hist, long long n, float* __restrict__ feat) {
+    const int b = blockIdx.x;
+    const unsigned* h = hist + (size_t)b * 768;
+    float* f = feat + (size_t)b * kFeat;
+    __shared__ double s1[3], s2[3];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < kFeat; i += 256) f[i] = 0.f;
+    if (w < 3) {
+        double a = 0, q = 0;
+        for (int v = lane; v < 256; v += 32) {
+            const float x = __fdiv_rn((float)v, 255.0f);
+            const double c = (double)h[w * 256 + v];
+            a += c * (double)x;
+            q += c * (double)__fmul_rn(x, x);          // img ** 2 is a float32 array (VGG:458)
+        }
+        a = warp_sum_f64(a); q = warp_sum_f64(q);
+        if (lane == 0) { s1[w] = a; s2[w] = q; }
+    }
+    __syncthreads();
+    if (w < 3) {
+        const double mean = s1[w] / (double)n;
+        double var = 0;
+        for (int v = lane; v < 256; v += 32) {
+            const double d = (double)__fdiv_rn((float)v, 255.0f) - mean;
+            var += (double)h[w * 256 + v] * d * d;
+        }
+        var = warp_sum_f64(var);
+        if (lane == 0) {
+            int vmin = 0, vmax = 255;
+            while (vmin < 255 && h[w * 256 + vmin] == 0) ++vmin;
+            while (vmax > 0 && h[w * 256 + vmax] == 0) --vmax;
+            // np.median: mean of the two middle order statistics (the same one when n is odd)
+            const long long k0 = (n - 1) / 2, k1 = n / 2;
+            long long acc = 0; int m0 = -1, m1 = -1;
+            for (int v = 0; v < 256 && m1 < 0; ++v) {
+                acc += h[w * 256 + v];
+                if (m0 < 0 && acc > k0) m0 = v;
+                if (acc > k1) m1 = v;
+            }
+            const float x0 = __fdiv_rn((float)m0, 255.0f), x1 = __fdiv_rn((float)m1, 255.0f);
+            f[w * 5 + 0] = (float)mean;
+            f[w * 5 + 1] = (float)sqrt(var / (double)n);
+            f[w * 5 + 2] = __fdiv_rn((float)vmin, 255.0f);
+            f[w * 5 + 3] = __fdiv_rn((float)vmax, 255.0f);
+            f[w * 5 + 4] = m0 == m1 ? x0 : __fdiv_rn(__fadd_rn(x0, x1), 2.0f);
+        }
+    }
+    __syncthreads();
+    if (w == 3) {                                      // overall mean, std, second moment (VGG:455-459)
+        const double tot = 3.0 * (double)n;
+        const double mean = (s1[0] + s1[1] + s1[2]) / tot;
+        double var = 0;
+        for (int i = lane; i < 768; i += 32) {
+            const double d = (double)__fdiv_rn((float)(i & 255), 255.0f) - mean;
+            var += (double)h[i] * d * d;
+        }
+        var = warp_sum_f64(var);
+        if (lane == 0) {
+            f[15] = (float)mean;
+            f[16] = (float)sqrt(var / tot);
+            f[17] = (float)((s2[0] + s2[1] + s2[2]) / tot);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- 224 x 224 network input
+// cv2.resize(uint8, INTER_LINEAR) in OpenCV's 11-bit fixed point, / 255, ImageNet
+// normalisation (torchvision Normalize: (x - mean) / std in float32), HWC -> CHW.
+struct ResizeTap { int s; int c1; };
+__device__ __forceinline__ ResizeTap resize_tap(int i, double scale, int n) {
+    float f = (float)(((double)i + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= (float)s;
+    if (s < 0) { s = 0; f = 0.f; }
+    if (s >= n - 1) { s = n - 1; f = 0.f; }
+    ResizeTap t; t.s = s; t.c1 = __float2int_rn(f * 2048.0f);
+    return t;
+}
+
+template <class In>
+__device__ __forceinline__ int load_byte(const In* p);
+template <> __device__ __forceinline__ int load_byte<uint8_t>(const uint8_t* p) { return *p; }
+template <> __device__ __forceinline__ int load_byte<float>(const float* p) { return (int)(uint8_t)(int)__fmul_rn(*p, 255.0f); }   // (img * 255).astype(np.uint8)
+
+template <class In>
+__global__ void __launch_bounds__(NT) vgg_preprocess_kernel(const In* __restrict__ frames, int H, int W, int size,
+                                                            float* __restrict__ out) {
+    const int b = blockIdx.y;
+    const int i = blockIdx.x * NT + threadIdx.x;
+    if (i >= size * size) return;
+    const int oy = i / size, ox = i - oy * size;
+    if (H == 2 * size && W == 2 * size) {
+        // cv2.resize turns INTER_LINEAR into INTER_AREA for an exact 2x decimation: rounded 2x2 mean
+        const In* f2 = frames + (size_t)b * H * W * 3;
+        const float mean2[3] = {0.485f, 0.456f, 0.406f}, std2[3] = {0.229f, 0.224f, 0.225f};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const In* q = f2 + ((size_t)(2 * oy) * W + 2 * ox) * 3 + c;
+            const int v = (load_byte<In>(q) + load_byte<In>(q + 3) + load_byte<In>(q + (size_t)W * 3) + load_byte<In>(q + (size_t)W * 3 + 3) + 2) >> 2;
+            out[((size_t)b * 3 + c) * size * size + i] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)v, 255.0f), mean2[c]), std2[c]);
+        }
+        return;
+    }
+    const ResizeTap ty = resize_tap(oy, (double)H / (double)size, H);
+    const ResizeTap tx = resize_tap(ox, (double)W / (double)size, W);
+    const int y1 = min(ty.s + 1, H - 1), x1 = min(tx.s + 1, W - 1);
+    const In* f = frames + (size_t)b * H * W * 3;
+    const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const int p00 = load_byte<In>(f + ((size_t)ty.s * W + tx.s) * 3 + c), p01 = load_byte<In>(f + ((size_t)ty.s * W + x1) * 3 + c);
+        const int p10 = load_byte<In>(f + ((size_t)y1 * W + tx.s) * 3 + c), p11 = load_byte<In>(f + ((size_t)y1 * W + x1) * 3 + c);
+        const int s0 = p00 * (2048 - tx.c1) + p01 * tx.c1;
+        const int s1 = p10 * (2048 - tx.c1) + p11 * tx.c1;
+        const int v = ((((2048 - ty.c1) * (s0 >> 4)) >> 16) + ((ty.c1 * (s1 >> 4)) >> 16) + 2) >> 2;
+        const float x = __fdiv_rn((float)min(max(v, 0), 255), 255.0f);
+        out[((size_t)b * 3 + c) * size * size + i] = __fdiv_rn(__fsub_rn(x, mean[c]), stdv[c]);
+    }
+}
+
+struct VggLayout { size_t state, prm, hist, total; };
+VggLayout vgg_layout(int batch) {
+    VggLayout L;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t at = off; off += (bytes + 255) & ~(size_t)255; return at; };
+    L.state = take((size_t)batch * 3 * kTargets * sizeof(SelState));
+    L.prm = take((size_t)batch * sizeof(EnhanceParams));
+    // the widest use: pass 1 of the selection (planes x targets x 2048 bins); features need batch x 768
+    L.hist = take((size_t)batch * 3 * kTargets * kBinsAB * 4);
+    L.total = off;
+    return L;
+}
+
+#define CUV(call)                                                                                  \
+    do {                                                                                           \
+        cudaError_t _e = (call);                                                                   \
+        if (_e != cudaSuccess) return uwie_fail(UWIE_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
+
+int grid_for(long long items) {
+    long long g = (items + NT * 8 - 1) / (NT * 8);
+    if (g < 1) g = 1;
+    if (g > 148 * 8) g = 148 * 8;
+    return (int)g;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t uwie_vgg_workspace_bytes(int batch) { return batch < 1 ? 0 : vgg_layout(batch).total; }
+
+int uwie_vgg_enhance(const float* img_dev, int batch, int height, int width, const float* l_low, const float* l_high,
+                     const float* omega, const float* gamma, float* out_dev, void* workspace_dev,
+                     size_t workspace_bytes, void* stream) {
+    if (!img_dev || !out_dev || !l_low || !l_high || batch < 1 || height < 1 || width < 1)
+        return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance: bad arguments");
+    const VggLayout L = vgg_layout(batch);
+    if (!workspace_dev || workspace_bytes < L.total) return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)workspace_dev;
+    const long long n = (long long)height * width;
+    // ranks: int(L / 100.0 * n) clamped to [0, n - 1], in Python float (double) arithmetic (VGG:78-82)
+    std::vector<SelState> hs((size_t)batch * 3 * kTargets);
+    std::vector<EnhanceParams> hp(batch);
+    for (int b = 0; b < batch; ++b) {
+        long long lo = (long long)(((double)l_low[b] / 100.0) * (double)n);
+        long long hi = (long long)(((double)l_high[b] / 100.0) * (double)n);
+        lo = lo < 0 ? 0 : (lo > n - 1 ? n - 1 : lo);
+        hi = hi < 0 ? 0 : (hi > n - 1 ? n - 1 : hi);
+        for (int c = 0; c < 3; ++c) {
+            hs[(size_t)(b * 3 + c) * kTargets + 0] = SelState{lo, 0u, 0.f};
+            hs[(size_t)(b * 3 + c) * kTargets + 1] = SelState{hi, 0u, 0.f};
+        }
+        hp[b].omega = omega ? omega[b] : 0.f;
+        hp[b].gamma = gamma ? gamma[b] : 1.f;
+    }
+    SelState* state = (SelState*)(ws + L.state);
+    EnhanceParams* prm = (EnhanceParams*)(ws + L.prm);
+    unsigned* hist = (unsigned*)(ws + L.hist);
+    // pageable sources: the runtime stages them before returning, so the vectors may die with this frame
+    CUV(cudaMemcpyAsync(state, hs.data(), hs.size() * sizeof(SelState), cudaMemcpyHostToDevice, st));
+    CUV(cudaMemcpyAsync(prm, hp.data(), hp.size() * sizeof(EnhanceParams), cudaMemcpyHostToDevice, st));
+    CUV(cudaMemsetAsync(hist, 0, (size_t)batch * 3 * kTargets * kBinsAB * 4, st));
+    const int planes = batch * 3;
+    const dim3 grid(grid_for(n / 4 + 1), planes);
+    vgg_sel_hist_kernel<0><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
+    vgg_sel_scan_kernel<0><<<planes, NT, 0, st>>>(state, hist);
+    vgg_sel_hist_kernel<1><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
+    vgg_sel_scan_kernel<1><<<planes, NT, 0, st>>>(state, hist);
+    vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
+    vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist);
+    vgg_enhance_kernel<<<dim3(grid_for(n / 4 + 1), batch), NT, 0, st>>>(img_dev, out_dev, n, state, prm, omega ? 1 : 0, gamma ? 1 : 0);
+    CUV(cudaGetLastError());
+    return UWIE_OK;
+}
+
+int uwie_vgg_features_u8(const uint8_t* frames_dev, int batch, int height, int width, float* feat_dev,
+                         void* workspace_dev, size_t workspace_bytes, void* stream) {
+    if (!frames_dev || !feat_dev || batch < 1 || height < 1 || width < 1)
+        return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_features_u8: bad arguments");
+    const VggLayout L = vgg_layout(batch);
+    if (!workspace_dev || workspace_bytes < L.total) return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_features_u8: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned* hist = (unsigned*)((char*)workspace_dev + L.hist);
+    CUV(cudaMemsetAsync(hist, 0, (size_t)batch * 768 * 4, st));
+    launch_frame_hist(frames_dev, batch, height, width, hist, st);
+    vgg_features_kernel<<<batch, 256, 0, st>>>(hist, (long long)height * width, feat_dev);
+    CUV(cudaGetLastError());
+    return UWIE_OK;
+}
+
+static int vgg_preprocess_check(const void* in, const void* out, int batch, int height, int width, int size) {
+    if (!in || !out || batch < 1 || height < 1 || width < 1 || size < 1)
+        return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_preprocess: bad arguments");
+    return UWIE_OK;
+}
+
+int uwie_vgg_preprocess_u8(const uint8_t* frames_dev, int batch, int height, int width, int size, float* out_dev, void* stream) {
+    if (int rc = vgg_preprocess_check(frames_dev, out_dev, batch, height, width, size)) return rc;
+    vgg_preprocess_kernel<uint8_t><<<dim3((size * size + NT - 1) / NT, batch), NT, 0, (cudaStream_t)stream>>>(frames_dev, height, width, size, out_dev);
+    CUV(cudaGetLastError());
+    return UWIE_OK;
+}
+
+int uwie_vgg_preprocess_f32(const float* img_dev, int batch, int height, int width, int size, float* out_dev, void* stream) {
+    if (int rc = vgg_preprocess_check(img_dev, out_dev, batch, height, width, size)) return rc;
+    vgg_preprocess_kernel<float><<<dim3((size * size + NT - 1) / NT, batch), NT, 0, (cudaStream_t)stream>>>(img_dev, height, width, size, out_dev);
+    CUV(cudaGetLastError());
+    return UWIE_OK;
+}
+
+}  // extern "C"

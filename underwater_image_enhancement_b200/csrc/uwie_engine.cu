@@ -21,6 +21,11 @@ namespace {
 thread_local std::string g_err;
 
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
+}  // namespace
+namespace uwie {
+int uwie_fail(int code, const std::string& msg) { return fail(code, msg); }   // for the other C-ABI files
+}
+namespace {
 
 #define CU(call)                                                                          \
     do {                                                                                  \

@@ -1,0 +1,113 @@
+"""Host-side mirror of the VGG-guided path's per-pixel pieces (use_trained_model.py / vgg_16_UIE.py).
+
+Same names and argument meaning as the reference; all arithmetic runs in libuwie_b200.so (uwie_vgg_*),
+PyTorch only provides device memory and the current stream.  The network (ImprovedVGGParameterNet)
+is not part of this package: it stays stock PyTorch (out of scope).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _stream(dev):
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _workspace(batch, dev):
+    need = _lib.load().uwie_vgg_workspace_bytes(int(batch))
+    return torch.empty(need, dtype=torch.uint8, device=dev), need
+
+
+def _floats(x, batch, name):
+    """(B,1) / (B,) tensor, sequence or scalar -> ctypes float array of length B (host side, like .item())."""
+    if x is None:
+        return None
+    if isinstance(x, torch.Tensor):
+        x = x.detach().reshape(-1).to("cpu", torch.float32).numpy()
+    arr = np.asarray(x, dtype=np.float32).reshape(-1)
+    if arr.size == 1 and batch > 1:
+        arr = np.repeat(arr, batch)
+    if arr.size != batch:
+        raise ValueError(f"{name}: expected {batch} values, got {arr.size}")
+    return (C.c_float * batch)(*arr.tolist())
+
+
+class DifferentiableEnhancement:
+    """vgg_16_UIE.py:24-128, inference only: forward(img, params) on a CUDA float32 NCHW batch."""
+
+    def forward(self, img: torch.Tensor, params: dict) -> torch.Tensor:
+        if not (isinstance(img, torch.Tensor) and img.is_cuda):
+            raise ValueError("img must be a CUDA tensor: the enhancement has no CPU path")
+        if img.dim() != 4 or img.shape[1] != 3:
+            raise ValueError(f"img must be (B, 3, H, W), got {tuple(img.shape)}")
+        img = img.contiguous().to(torch.float32)
+        B, _, H, W = img.shape
+        lo = _floats(params["L_low"], B, "L_low")                      # KeyError like the reference
+        hi = _floats(params["L_high"], B, "L_high")
+        om = _floats(params.get("omega"), B, "omega")
+        ga = _floats(params.get("gamma"), B, "gamma")
+        out = torch.empty_like(img)
+        ws, need = _workspace(B, img.device)
+        with torch.cuda.device(img.device):
+            _lib.check(_lib.load().uwie_vgg_enhance(C.c_void_p(img.data_ptr()), B, H, W, lo, hi, om, ga,
+                                                    C.c_void_p(out.data_ptr()), C.c_void_p(ws.data_ptr()), need,
+                                                    _stream(img.device)))
+        ws.record_stream(torch.cuda.current_stream(img.device))
+        return out
+
+    __call__ = forward
+
+
+def _frames_u8(img, device):
+    """HWC or BHWC uint8 image(s), NumPy or torch -> contiguous CUDA uint8 [B,H,W,3]."""
+    t = torch.as_tensor(img) if not isinstance(img, torch.Tensor) else img
+    if t.dim() == 3:
+        t = t[None]
+    if t.dim() != 4 or t.shape[-1] != 3:
+        raise ValueError(f"expected (H, W, 3) or (B, H, W, 3), got {tuple(t.shape)}")
+    return t.to(device).contiguous()
+
+
+def extract_all_features(img, device="cuda:0") -> torch.Tensor:
+    """vgg_16_UIE.py:435-466 for uint8 RGB frame(s): float32 [B, 79] on the device.
+
+    The reference's only caller (use_trained_model.py:55) passes imread / 255; pass the bytes themselves
+    (the reference divides uint8 input by 255 itself, VGG:425-433)."""
+    t = torch.as_tensor(img) if not isinstance(img, torch.Tensor) else img
+    if t.dtype != torch.uint8:
+        raise TypeError("extract_all_features takes the uint8 frame (float32 k/255 images: pass the bytes)")
+    frames = _frames_u8(t, device)
+    B, H, W, _ = frames.shape
+    feat = torch.empty((B, _lib.VGG_FEATURES), dtype=torch.float32, device=frames.device)
+    ws, need = _workspace(B, frames.device)
+    with torch.cuda.device(frames.device):
+        _lib.check(_lib.load().uwie_vgg_features_u8(C.c_void_p(frames.data_ptr()), B, H, W, C.c_void_p(feat.data_ptr()),
+                                                    C.c_void_p(ws.data_ptr()), need, _stream(frames.device)))
+    ws.record_stream(torch.cuda.current_stream(frames.device))
+    return feat
+
+
+def preprocess_for_vgg(img, input_size: int = 224, device="cuda:0") -> torch.Tensor:
+    """use_trained_model.py:39-46 for uint8 or float32 [0,1] HWC frame(s): float32 [B, 3, size, size]."""
+    t = torch.as_tensor(img) if not isinstance(img, torch.Tensor) else img
+    if t.dim() == 3:
+        t = t[None]
+    if t.dim() != 4 or t.shape[-1] != 3:
+        raise ValueError(f"expected (H, W, 3) or (B, H, W, 3), got {tuple(t.shape)}")
+    if t.dtype == torch.uint8:
+        fn = _lib.load().uwie_vgg_preprocess_u8
+    elif t.dtype == torch.float32:
+        fn = _lib.load().uwie_vgg_preprocess_f32
+    else:
+        raise TypeError(f"unsupported dtype {t.dtype}")
+    t = t.to(device).contiguous()
+    B, H, W, _ = t.shape
+    out = torch.empty((B, 3, input_size, input_size), dtype=torch.float32, device=t.device)
+    with torch.cuda.device(t.device):
+        _lib.check(fn(C.c_void_p(t.data_ptr()), B, H, W, int(input_size), C.c_void_p(out.data_ptr()), _stream(t.device)))
+    return out
