@@ -267,14 +267,23 @@ __global__ void __launch_bounds__(256) vgg_features_kernel(const unsigned* __res
 // ---------------------------------------------------------------- 224 x 224 network input
 // cv2.resize(uint8, INTER_LINEAR) in OpenCV's 11-bit fixed point, / 255, ImageNet
 // normalisation (torchvision Normalize: (x - mean) / std in float32), HWC -> CHW.
-struct ResizeTap { int s; int c1; };
-__device__ __forceinline__ ResizeTap resize_tap(int i, double scale, int n) {
+struct ResizeTap { int s0, s1; int c1; };
+// horizontal taps: a source index outside the row is clamped AND its fraction zeroed; vertical taps keep
+// the fraction and only clamp the two row indices (cv2's resize treats the two directions differently,
+// which shows in the first / last rows of an upscale because the two products are truncated separately)
+__device__ __forceinline__ ResizeTap resize_tap(int i, double scale, int n, bool vertical) {
     float f = (float)(((double)i + 0.5) * scale - 0.5);
     int s = (int)floorf(f);
     f -= (float)s;
-    if (s < 0) { s = 0; f = 0.f; }
-    if (s >= n - 1) { s = n - 1; f = 0.f; }
-    ResizeTap t; t.s = s; t.c1 = __float2int_rn(f * 2048.0f);
+    ResizeTap t;
+    if (vertical) {
+        t.s0 = min(max(s, 0), n - 1); t.s1 = min(max(s + 1, 0), n - 1);
+    } else {
+        if (s < 0) { s = 0; f = 0.f; }
+        if (s >= n - 1) { s = n - 1; f = 0.f; }
+        t.s0 = s; t.s1 = min(s + 1, n - 1);
+    }
+    t.c1 = __float2int_rn(f * 2048.0f);
     return t;
 }
 
@@ -302,15 +311,14 @@ __global__ void __launch_bounds__(NT) vgg_preprocess_kernel(const In* __restrict
         }
         return;
     }
-    const ResizeTap ty = resize_tap(oy, (double)H / (double)size, H);
-    const ResizeTap tx = resize_tap(ox, (double)W / (double)size, W);
-    const int y1 = min(ty.s + 1, H - 1), x1 = min(tx.s + 1, W - 1);
+    const ResizeTap ty = resize_tap(oy, (double)H / (double)size, H, true);
+    const ResizeTap tx = resize_tap(ox, (double)W / (double)size, W, false);
     const In* f = frames + (size_t)b * H * W * 3;
     const float mean[3] = {0.485f, 0.456f, 0.406f}, stdv[3] = {0.229f, 0.224f, 0.225f};
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        const int p00 = load_byte<In>(f + ((size_t)ty.s * W + tx.s) * 3 + c), p01 = load_byte<In>(f + ((size_t)ty.s * W + x1) * 3 + c);
-        const int p10 = load_byte<In>(f + ((size_t)y1 * W + tx.s) * 3 + c), p11 = load_byte<In>(f + ((size_t)y1 * W + x1) * 3 + c);
+        const int p00 = load_byte<In>(f + ((size_t)ty.s0 * W + tx.s0) * 3 + c), p01 = load_byte<In>(f + ((size_t)ty.s0 * W + tx.s1) * 3 + c);
+        const int p10 = load_byte<In>(f + ((size_t)ty.s1 * W + tx.s0) * 3 + c), p11 = load_byte<In>(f + ((size_t)ty.s1 * W + tx.s1) * 3 + c);
         const int s0 = p00 * (2048 - tx.c1) + p01 * tx.c1;
         const int s1 = p10 * (2048 - tx.c1) + p11 * tx.c1;
         const int v = ((((2048 - ty.c1) * (s0 >> 4)) >> 16) + ((ty.c1 * (s1 >> 4)) >> 16) + 2) >> 2;
