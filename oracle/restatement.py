@@ -498,3 +498,184 @@ def vgg_preprocess(img: np.ndarray, size: int = 224) -> np.ndarray:
     mean = np.array([0.485, 0.456, 0.406], np.float32).reshape(3, 1, 1)
     std = np.array([0.229, 0.224, 0.225], np.float32).reshape(3, 1, 1)
     return ((chw - mean) / std).astype(np.float32)
+
+
+# ----------------------------------------------------------------------------------------
+# FE = feature_extraction.py: the 79 hand-crafted features
+# Order: colour 35 | texture 22 | frequency 5 | edge 7 | quality 10   (FE:249-297)
+# The three scikit-image functions of the texture group are restated from their documented
+# algorithm; scikit-image is not installable here, so that group is UNPINNED.
+# ----------------------------------------------------------------------------------------
+
+
+def sk_local_binary_pattern_uniform(image: np.ndarray, P: int = 8, R: float = 1.0) -> np.ndarray:
+    """skimage.feature.local_binary_pattern(image, P, R, method='uniform') (FE:97), float64 output.
+
+    Taps at (-R sin(2 pi p / P), R cos(2 pi p / P)) rounded to 5 decimals; bilinear interpolation in
+    double with constant 0 outside the image; bit = tap >= centre; code = number of set bits when the
+    bit string has at most two transitions between its P - 1 adjacent pairs (not circular), else P + 1."""
+    img = np.ascontiguousarray(image, dtype=np.float64)
+    rows, cols = img.shape
+    ang = 2.0 * np.pi * np.arange(P, dtype=np.float64) / P
+    rp = np.round(-R * np.sin(ang), 5)
+    cp = np.round(R * np.cos(ang), 5)
+    pad = np.zeros((rows + 4, cols + 4), np.float64)
+    pad[2:-2, 2:-2] = img
+    rr, cc = np.meshgrid(np.arange(rows, dtype=np.float64), np.arange(cols, dtype=np.float64), indexing="ij")
+    bits = np.zeros((P, rows, cols), np.int64)
+    for p in range(P):
+        r, c = rr + rp[p], cc + cp[p]
+        r0, c0 = np.floor(r), np.floor(c)
+        dr, dc = r - r0, c - c0
+        i0, j0 = r0.astype(np.int64) + 2, c0.astype(np.int64) + 2
+        tl, tr = pad[i0, j0], pad[i0, j0 + 1]
+        bl, br = pad[i0 + 1, j0], pad[i0 + 1, j0 + 1]
+        top = (1 - dc) * tl + dc * tr
+        bot = (1 - dc) * bl + dc * br
+        bits[p] = ((1 - dr) * top + dr * bot - img) >= 0
+    changes = np.zeros((rows, cols), np.int64)
+    for p in range(P - 1):
+        changes += bits[p] != bits[p + 1]
+    return np.where(changes <= 2, bits.sum(axis=0), P + 1).astype(np.float64)
+
+
+_GLCM_OFFSETS = ((0, 1), (1, 1), (1, 0), (1, -1))   # (round(sin a), round(cos a)) for a = 0, pi/4, pi/2, 3pi/4
+
+
+def sk_graycomatrix(image: np.ndarray, levels: int = 256) -> np.ndarray:
+    """graycomatrix(image, [1], [0, pi/4, pi/2, 3pi/4], levels, symmetric=True, normed=True) (FE:107-112):
+    float64 [levels, levels, 1, 4]; offset of angle a is (round(sin a), round(cos a)) with rows counted
+    downwards, in-bounds pairs only."""
+    img = np.asarray(image)
+    rows, cols = img.shape
+    out = np.zeros((levels, levels, 1, 4), np.float64)
+    for k, (dr, dc) in enumerate(_GLCM_OFFSETS):
+        r0, r1 = max(0, -dr), rows - max(0, dr)
+        c0, c1 = max(0, -dc), cols - max(0, dc)
+        a = img[r0:r1, c0:c1].reshape(-1).astype(np.int64)
+        b = img[r0 + dr:r1 + dr, c0 + dc:c1 + dc].reshape(-1).astype(np.int64)
+        m = np.bincount(a * levels + b, minlength=levels * levels).reshape(levels, levels).astype(np.float64)
+        m = m + m.T
+        out[:, :, 0, k] = m / m.sum()
+    return out
+
+
+def sk_graycoprops(P: np.ndarray, prop: str) -> np.ndarray:
+    """graycoprops (FE:117): [1, 4] array of one property per (distance, angle)."""
+    levels = P.shape[0]
+    I, J = np.ogrid[0:levels, 0:levels]
+    I = I.reshape(levels, 1, 1, 1).astype(np.float64)
+    J = J.reshape(1, levels, 1, 1).astype(np.float64)
+    if prop == "contrast":
+        return np.sum(P * (I - J) ** 2, axis=(0, 1))
+    if prop == "dissimilarity":
+        return np.sum(P * np.abs(I - J), axis=(0, 1))
+    if prop == "homogeneity":
+        return np.sum(P / (1.0 + (I - J) ** 2), axis=(0, 1))
+    asm = np.sum(P ** 2, axis=(0, 1))
+    if prop == "ASM":
+        return asm
+    if prop == "energy":
+        return np.sqrt(asm)
+    if prop == "correlation":
+        mi = np.sum(I * P, axis=(0, 1))
+        mj = np.sum(J * P, axis=(0, 1))
+        si = np.sqrt(np.sum(P * (I - mi) ** 2, axis=(0, 1)))
+        sj = np.sqrt(np.sum(P * (J - mj) ** 2, axis=(0, 1)))
+        cov = np.sum(P * (I - mi) * (J - mj), axis=(0, 1))
+        res = np.ones_like(cov)
+        ok = ~((si < 1e-15) | (sj < 1e-15))
+        res[ok] = cov[ok] / (si[ok] * sj[ok])
+        return res
+    raise ValueError(prop)
+
+
+GLCM_PROPS = ("contrast", "dissimilarity", "homogeneity", "energy", "correlation", "ASM")   # FE:115
+
+
+def _moments4(x: np.ndarray):
+    """mean, std, skew, kurtosis the way FE:33-40 asks for them (np / scipy.stats on a float32 vector)."""
+    from scipy import stats
+    return [np.mean(x), np.std(x), stats.skew(x), stats.kurtosis(x)]
+
+
+def fe_color(img: np.ndarray) -> np.ndarray:
+    """extract_color_features (FE:17-77): 35 values."""
+    q = quantise_u8(img)
+    lab = cv2.cvtColor(q, cv2.COLOR_RGB2LAB).astype(np.float32)
+    hsv = cv2.cvtColor(q, cv2.COLOR_RGB2HSV).astype(np.float32)
+    out = []
+    for c in range(3):
+        out += _moments4(lab[:, :, c].reshape(-1))
+    for c in range(3):
+        ch = hsv[:, :, c].reshape(-1)
+        out += [np.mean(ch), np.std(ch)]
+    a, b = lab[:, :, 1], lab[:, :, 2]
+    ma, mb = np.mean(a), np.mean(b)
+    M = np.sqrt(ma ** 2 + mb ** 2)
+    D = np.sqrt(np.mean(np.abs(a - ma)) ** 2 + np.mean(np.abs(b - mb)) ** 2)
+    out += [M / (D + 1e-10), M, D, ma, mb]
+    for c in range(3):
+        ch = img[:, :, c].reshape(-1)
+        out += [np.mean(ch), np.std(ch), np.min(ch), np.max(ch)]
+    return np.array(out)
+
+
+def fe_texture(img: np.ndarray) -> np.ndarray:
+    """extract_texture_features (FE:80-120): LBP histogram (10) + GLCM statistics (12)."""
+    gray = gray_u8(img).astype(np.float32) / 255.0
+    g8 = (gray * 255).astype(np.uint8)
+    lbp = sk_local_binary_pattern_uniform(g8, 8, 1)
+    hist, _ = np.histogram(lbp.ravel(), bins=10, range=(0, 10), density=True)
+    small = cv2.resize(g8, (128, 128))
+    P = sk_graycomatrix(small, 256)
+    out = list(hist)
+    for prop in GLCM_PROPS:
+        v = sk_graycoprops(P, prop).reshape(-1)
+        out += [np.mean(v), np.std(v)]
+    return np.array(out)
+
+
+def fe_frequency(img: np.ndarray) -> np.ndarray:
+    """extract_frequency_features (FE:123-158): DCT energy split + |DCT| statistics."""
+    d = cv2.dct(gray_u8(img).astype(np.float32))
+    h, w = d.shape
+    total = np.sum(d ** 2)
+    return np.array([np.sum(d[:h // 4, :w // 4] ** 2) / total,
+                     np.sum(d[h // 4:h // 2, w // 4:w // 2] ** 2) / total,
+                     np.sum(d[h // 2:, w // 2:] ** 2) / total,
+                     np.mean(np.abs(d)), np.std(np.abs(d))])
+
+
+def fe_edge(img: np.ndarray) -> np.ndarray:
+    """extract_edge_features (FE:161-200)."""
+    gray = gray_u8(img).astype(np.float32) / 255.0
+    sx = cv2.Sobel(gray, cv2.CV_32F, 1, 0, ksize=3)
+    sy = cv2.Sobel(gray, cv2.CV_32F, 0, 1, ksize=3)
+    mag = np.sqrt(sx ** 2 + sy ** 2)
+    g8 = (gray * 255).astype(np.uint8)
+    edges = cv2.Canny(g8, 50, 150)
+    lap = cv2.Laplacian(g8, cv2.CV_64F, ksize=3)
+    return np.array([np.mean(mag), np.std(mag), np.max(mag), np.sum(edges > 0) / edges.size,
+                     np.mean(np.abs(lap)), np.std(lap), np.var(lap)])
+
+
+def fe_quality(img: np.ndarray) -> np.ndarray:
+    """extract_quality_features (FE:203-246)."""
+    q = quantise_u8(img)
+    gray = cv2.cvtColor(q, cv2.COLOR_RGB2GRAY).astype(np.float32) / 255.0
+    sat = cv2.cvtColor(q, cv2.COLOR_RGB2HSV).astype(np.float32)[:, :, 1] / 255.0
+    return np.array([np.std(gray), _value_entropy(gray), np.mean(gray), np.median(gray),
+                     np.percentile(gray, 25), np.percentile(gray, 75), np.max(gray) - np.min(gray),
+                     np.mean(sat), np.std(sat), np.sqrt(np.mean((gray - np.mean(gray)) ** 2))])
+
+
+FE_GROUPS = (("color", fe_color, 35), ("texture", fe_texture, 22), ("frequency", fe_frequency, 5),
+             ("edge", fe_edge, 7), ("quality", fe_quality, 10))
+
+
+def fe_all(img: np.ndarray) -> np.ndarray:
+    """extract_all_features (FE:249-297): concatenation of the five groups, float64 [79]."""
+    if img.dtype == np.uint8:
+        img = to_unit_f32(img)
+    return np.concatenate([np.asarray(fn(img), dtype=np.float64) for _, fn, _ in FE_GROUPS])
