@@ -164,6 +164,19 @@ int uwie_vgg_preprocess_u8(const uint8_t* frames_dev, int batch, int height, int
 int uwie_vgg_preprocess_f32(const float* img_dev, int batch, int height, int width, int size,
                             float* out_dev, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * feature_extraction.py: FeatureExtractor.extract_all_features (FE:249-297) of uint8 RGB frames
+ * [batch][H][W][3] on the device -> float64 [batch][79]:
+ *   colour 35 (FE:17-77) | texture 22 (FE:80-120) | frequency 5 (FE:123-158) | edge 7 (FE:161-200) |
+ *   quality 10 (FE:203-246).
+ * Stateless, asynchronous on `stream`; `workspace_dev` must hold uwie_features79_workspace_bytes(...).
+ * The DCT of the frequency group runs as two float32 GEMMs through cuBLAS.
+ * ------------------------------------------------------------------------------------------- */
+#define UWIE_FEATURES 79
+size_t uwie_features79_workspace_bytes(int batch, int height, int width);
+int uwie_features79(const uint8_t* frames_dev, int batch, int height, int width, double* feat_dev,
+                    void* workspace_dev, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
