@@ -165,6 +165,17 @@ int uwie_vgg_preprocess_f32(const float* img_dev, int batch, int height, int wid
                             float* out_dev, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * quality_assessment.py: QualityAssessment.comprehensive_assessment(img, weights) (QA:215-286) of
+ * images that did not come out of an engine.  img_dev: [batch][H][W][3] on the device, dtype 0 = uint8
+ * (the image is bytes / 255 in float32), 1 = float32, 2 = float64 (the enhanced image in [0, 1]);
+ * weights: HOST array of 8 doubles in QA key order; scores_dev: double [batch][UWIE_SCORE_COLS].
+ * Stateless, asynchronous on `stream`.
+ * ------------------------------------------------------------------------------------------- */
+size_t uwie_quality_workspace_bytes(int batch, int height, int width);
+int uwie_quality_scores(const void* img_dev, int dtype, int batch, int height, int width, const double* weights,
+                        double* scores_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * feature_extraction.py: FeatureExtractor.extract_all_features (FE:249-297) of uint8 RGB frames
  * [batch][H][W][3] on the device -> float64 [batch][79]:
  *   colour 35 (FE:17-77) | texture 22 (FE:80-120) | frequency 5 (FE:123-158) | edge 7 (FE:161-200) |

@@ -19,7 +19,7 @@ EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_byt
            "uwie_engine_last_launches", "uwie_engine_debug", "uwie_engine_profile",
            "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_features_u8",
            "uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32", "uwie_features79_workspace_bytes",
-           "uwie_features79")
+           "uwie_features79", "uwie_quality_workspace_bytes", "uwie_quality_scores")
 FEATURES = 79
 VGG_FEATURES = 79
 STAGE_NAME_LEN = 32
@@ -101,6 +101,11 @@ def load() -> C.CDLL:
     lib.uwie_features79_workspace_bytes.restype = C.c_size_t
     lib.uwie_features79.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.uwie_features79.restype = C.c_int
+    lib.uwie_quality_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.uwie_quality_workspace_bytes.restype = C.c_size_t
+    lib.uwie_quality_scores.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_void_p,
+                                        C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.uwie_quality_scores.restype = C.c_int
     _lib = lib
     return lib
 
