@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--library", default="six", choices=("six", "es"))
     ap.add_argument("--lanes", type=int, default=2,
                     help="engines (own workspace + stream each) that take the chunks of a step in turn")
-    ap.add_argument("--e2e-frames", type=int, default=64, help="frames per e2e step (host buffers)")
+    ap.add_argument("--e2e-frames", type=int, default=256, help="frames per e2e step (host buffers)")
     ap.add_argument("--cpu-frames", type=int, default=0, help="cpu_baseline sample size (0 = one per worker)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()

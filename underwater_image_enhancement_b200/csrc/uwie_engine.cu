@@ -84,7 +84,14 @@ struct uwie_engine {
         // pinned landing zone of the small results: a D2H copy into PAGEABLE memory blocks the host
         // until the stream gets there, which would serialise the whole pipeline
         char* h_small = nullptr; size_t h_small_frames = 0;
+        // second lane: odd chunks run on a twin engine (own workspace) and stream, so that the launch-
+        // and latency-bound stretches of one chunk (quadtree levels, table set-up, scoring) overlap the
+        // wide kernels of the other
+        uwie_engine* twin = nullptr; bool twin_failed = false;
+        cudaStream_t s_run2 = nullptr; cudaEvent_t ev_twin = nullptr;
     } pipe;
+    uwie_library pub_lib;                         // what the engine was created from (for the twin)
+    std::vector<uwie_strategy> pub_strategies;
     template <class T> T* at(size_t off) const { return reinterpret_cast<T*>(ws + off); }
 };
 
@@ -290,6 +297,8 @@ int uwie_engine_create(uwie_engine** out, const uwie_library* lib, const uwie_st
     uwie_engine* e = new uwie_engine();
     int rc = init_engine_shape(e, lib, st, n, B, H, W);
     if (rc) { delete e; return rc; }
+    e->pub_lib = *lib;
+    e->pub_strategies.assign(st, st + n);
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
         delete e;
@@ -338,6 +347,9 @@ void uwie_engine_destroy(uwie_engine* e) {
         if (hp.h_small) cudaFreeHost(hp.h_small);
         if (hp.s_in) cudaStreamDestroy(hp.s_in);
         if (hp.s_out) cudaStreamDestroy(hp.s_out);
+        if (hp.twin) uwie_engine_destroy(hp.twin);
+        if (hp.s_run2) cudaStreamDestroy(hp.s_run2);
+        if (hp.ev_twin) cudaEventDestroy(hp.ev_twin);
     }
     for (auto& m : e->marks) cudaEventDestroy(m.ev);
     for (auto& ev : e->ev_pool) cudaEventDestroy(ev);
@@ -594,10 +606,23 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
     int32_t* p_best = reinterpret_cast<int32_t*>(p_scores + (size_t)count * S * kScoreCols);
     int32_t* p_types = p_best + count;
     float* p_light = reinterpret_cast<float*>(p_types + count);
+    // second lane (see HostPipe): only worth its workspace when there is more than one chunk
+    if (count > (int)B && !hp.twin && !hp.twin_failed && !e->prof_on && !std::getenv("UWIE_HOST_ONE_LANE")) {
+        if (uwie_engine_create(&hp.twin, &e->pub_lib, e->pub_strategies.data(), (int)S, (int)B, e->H, e->W, nullptr, 0) != UWIE_OK ||
+            cudaStreamCreateWithFlags(&hp.s_run2, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&hp.ev_twin, cudaEventDisableTiming) != cudaSuccess) {
+            cudaGetLastError();
+            if (hp.twin) { uwie_engine_destroy(hp.twin); hp.twin = nullptr; }
+            hp.twin_failed = true;                   // e.g. no memory for a second workspace: one lane it is
+        }
+    }
+    const bool two_lanes = hp.twin && !e->prof_on && count > (int)B;
     // the copy streams must not start before work already queued on the caller's stream
     CU(cudaEventRecord(hp.ev_start, st));
     CU(cudaStreamWaitEvent(hp.s_in, hp.ev_start, 0));
     CU(cudaStreamWaitEvent(hp.s_out, hp.ev_start, 0));
+    if (two_lanes) CU(cudaStreamWaitEvent(hp.s_run2, hp.ev_start, 0));
+    int launches_total = 0;
     int chunk = 0;
     for (int done = 0; done < count; done += (int)B, ++chunk) {
         const int k = chunk & 1;
@@ -612,12 +637,15 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
                            cudaMemcpyHostToDevice, hp.s_in));
         CU(cudaEventRecord(hp.ev_in[k], hp.s_in));
         // kernels: need the frames, and the slot's result buffers drained (D2H of chunk - 2)
-        CU(cudaStreamWaitEvent(st, hp.ev_in[k], 0));
-        if (chunk >= 2) CU(cudaStreamWaitEvent(st, hp.ev_out[k], 0));
-        int rc = enqueue_batch(e, hp.frames[k], nb, out_all_host ? hp.out_all[k] : nullptr,
-                               out_best_host ? hp.best_img[k] : nullptr, d_scores, d_best, d_types, d_light, st);
+        uwie_engine* lane = (two_lanes && k) ? hp.twin : e;
+        cudaStream_t ls = (two_lanes && k) ? hp.s_run2 : st;
+        CU(cudaStreamWaitEvent(ls, hp.ev_in[k], 0));
+        if (chunk >= 2) CU(cudaStreamWaitEvent(ls, hp.ev_out[k], 0));
+        int rc = enqueue_batch(lane, hp.frames[k], nb, out_all_host ? hp.out_all[k] : nullptr,
+                               out_best_host ? hp.best_img[k] : nullptr, d_scores, d_best, d_types, d_light, ls);
         if (rc) return rc;
-        CU(cudaEventRecord(hp.ev_run[k], st));
+        launches_total += lane->last_launches;
+        CU(cudaEventRecord(hp.ev_run[k], ls));
         // D2H
         CU(cudaStreamWaitEvent(hp.s_out, hp.ev_run[k], 0));
         if (out_all_host)
@@ -631,7 +659,16 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
         if (light_host) CU(cudaMemcpyAsync(p_light + (size_t)done * 3, d_light, sizeof(float) * nb * 3, cudaMemcpyDeviceToHost, hp.s_out));
         CU(cudaEventRecord(hp.ev_out[k], hp.s_out));
     }
+    if (two_lanes) {                                  // the caller's stream is done when both lanes are
+        CU(cudaEventRecord(hp.ev_twin, hp.s_run2));
+        CU(cudaStreamWaitEvent(st, hp.ev_twin, 0));
+    }
     CU(cudaStreamSynchronize(hp.s_out));
+    e->last_launches = launches_total;
+    if (two_lanes) {
+        const int rc2 = uwie_engine_check(hp.twin, hp.s_run2);
+        if (rc2) return rc2;
+    }
     if (scores_host) std::memcpy(scores_host, p_scores, sizeof(double) * (size_t)count * S * kScoreCols);
     if (best_host) std::memcpy(best_host, p_best, sizeof(int) * (size_t)count);
     if (type_host) std::memcpy(type_host, p_types, sizeof(int) * (size_t)count);
