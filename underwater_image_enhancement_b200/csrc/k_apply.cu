@@ -107,78 +107,185 @@ __device__ __forceinline__ int clahe_interp(const uint8_t* luts, int tiles_x, in
 // ---------------------------------------------------------------- per-pixel tail of a strategy
 // FINAL = false: only the per-channel histograms of the CLAHE output (strategies with post-stretches)
 // FINAL = true : output bytes, gray plane, scoring accumulators
+// A block owns pix_per_block consecutive pixels; a thread takes 4 consecutive pixels at a time so that
+// frame bytes, recovered floats, output bytes and gray bytes move as 32 / 128-bit words.  The colour
+// tables and the strategy's byte tables are staged in shared memory once per block.
+struct ApplyShared {
+    ColorTables ct;                 // 10.5 KB
+    uint8_t preq[3][256];
+    uint8_t postq[3][256];
+};
+
+template <class T> struct Vec4 { T v[4][3]; };
+
 template <class T, bool FINAL>
 __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
     const int s = blockIdx.y, b = blockIdx.z;
     const Recipe& rc = a.recipes[s];
     if (!FINAL && !(rc.clahe && rc.n_post > 0)) return;
     const StratTables& st = a.tables[(size_t)b * a.S + s];
-    const size_t npix = (size_t)a.H * a.W;
+    const unsigned npix = (unsigned)a.H * (unsigned)a.W;
     const size_t bs = (size_t)b * a.S + s;
     __shared__ unsigned sh_a[3][256];     // HIST: channel histograms; FINAL: [0] gray, [1] saturation
+    __shared__ __align__(16) ApplyShared sm;
+    __shared__ T s_postf[3][256];
     for (int i = threadIdx.x; i < 768; i += NT) (&sh_a[0][0])[i] = 0;
+    {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(a.ctab);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&sm.ct);
+        for (int i = threadIdx.x; i < (int)(sizeof(ColorTables) / 4); i += NT) dst[i] = src[i];
+        for (int i = threadIdx.x; i < 768; i += NT) {
+            (&sm.preq[0][0])[i] = (&st.preq[0][0])[i];
+            (&sm.postq[0][0])[i] = (&st.postq[0][0])[i];
+            (&s_postf[0][0])[i] = (T)(&st.postf[0][0])[i];
+        }
+    }
+    const bool clahe = rc.clahe != 0, dehaze = rc.dehaze != 0;
+    const int n_pre = rc.n_pre;
+    T lo[kMaxStretch][3], den[kMaxStretch][3];
+#pragma unroll
+    for (int i = 0; i < kMaxStretch; ++i)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { lo[i][c] = (T)st.st_lo[i][c]; den[i][c] = (T)st.st_den[i][c]; }
     __syncthreads();
 
     TileGeo geo = {1, 1};
     float inv_tw = 0.f, inv_th = 0.f;
     const uint8_t* luts = a.tile_lut + bs * kMaxTiles * 256;
-    if (rc.clahe) {
-        geo = tile_geo(a.H, a.W, rc.tiles_x, rc.tiles_y);
+    const int tiles_x = rc.tiles_x, tiles_y = rc.tiles_y;
+    if (clahe) {
+        geo = tile_geo(a.H, a.W, tiles_x, tiles_y);
         inv_tw = __fdiv_rn(1.0f, (float)geo.tw);
         inv_th = __fdiv_rn(1.0f, (float)geo.th);
     }
-    const ColorTables* ct = a.ctab;
-    uint8_t* out = FINAL ? a.out + bs * npix * 3 : nullptr;
-    uint8_t* gray = FINAL ? a.gray + bs * npix : nullptr;
+    const uint8_t* frame = a.frames + (size_t)b * npix * 3;
+    const T* rec = dehaze ? reinterpret_cast<const T*>(a.recovered) + (size_t)(b * a.n_dehaze + a.dehaze_slot[s]) * npix * 3 : nullptr;
+    uint8_t* out = FINAL ? a.out + bs * (size_t)npix * 3 : nullptr;
+    uint8_t* gray = FINAL ? a.gray + bs * (size_t)npix : nullptr;
+    const bool words_ok = (reinterpret_cast<uintptr_t>(frame) & 3) == 0 &&
+                          (!FINAL || (((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(gray)) & 3) == 0));
     double m_rg = 0, m_rg2 = 0, m_yb = 0, m_yb2 = 0;
     unsigned long long lum = 0;
 
-    const size_t p0 = (size_t)blockIdx.x * a.pix_per_block;
-    const size_t p1 = min(p0 + (size_t)a.pix_per_block, npix);
-    for (size_t p = p0 + threadIdx.x; p < p1; p += NT) {
+    static_assert(kMaxStretch == 2, "pre_stretch is written out for two stretches");
+    auto pre_stretch = [&](T& v0, T& v1, T& v2) {          // static indices keep lo / den in registers
+        if (n_pre > 0) {
+            v0 = stretch_apply<T>(v0, lo[0][0], den[0][0]); v1 = stretch_apply<T>(v1, lo[0][1], den[0][1]);
+            v2 = stretch_apply<T>(v2, lo[0][2], den[0][2]);
+        }
+        if (n_pre > 1) {
+            v0 = stretch_apply<T>(v0, lo[1][0], den[1][0]); v1 = stretch_apply<T>(v1, lo[1][1], den[1][1]);
+            v2 = stretch_apply<T>(v2, lo[1][2], den[1][2]);
+        }
+    };
+    // one pixel: bytes (no-dehaze) or floats (dehaze) in -> float value f and byte q per channel out.
+    // Returns false when the pixel only feeds the HIST pass.
+    auto shade = [&](int r8, int g8, int b8, T fr, T fg, T fb, int y, int x, T* f, int* q) -> bool {
+        if (clahe) {
+            int r, g, bl, L, A, Bc;
+            if (!dehaze) { r = sm.preq[0][r8]; g = sm.preq[1][g8]; bl = sm.preq[2][b8]; }
+            else {
+                T v0 = fr, v1 = fg, v2 = fb;
+                pre_stretch(v0, v1, v2);
+                r = quantise<T>(v0); g = quantise<T>(v1); bl = quantise<T>(v2);
+            }
+            rgb_to_lab(sm.ct.gamma_in, sm.ct.cbrt_tab, r, g, bl, L, A, Bc);
+            L = clahe_interp(luts, tiles_x, tiles_y, inv_tw, inv_th, y, x, L);
+            int k0, k1, k2;
+            lab_to_rgb(sm.ct.lab_yf, sm.ct.gamma_out, L, A, Bc, k0, k1, k2);
+            if (!FINAL) {
+                atomicAdd(&sh_a[0][k0], 1u); atomicAdd(&sh_a[1][k1], 1u); atomicAdd(&sh_a[2][k2], 1u);
+                return false;
+            }
+            f[0] = s_postf[0][k0]; f[1] = s_postf[1][k1]; f[2] = s_postf[2][k2];
+            q[0] = sm.postq[0][k0]; q[1] = sm.postq[1][k1]; q[2] = sm.postq[2][k2];
+        } else if (!dehaze) {
+            f[0] = s_postf[0][r8]; f[1] = s_postf[1][g8]; f[2] = s_postf[2][b8];
+            q[0] = sm.postq[0][r8]; q[1] = sm.postq[1][g8]; q[2] = sm.postq[2][b8];
+        } else {
+            T v0 = fr, v1 = fg, v2 = fb;
+            pre_stretch(v0, v1, v2);
+            f[0] = apply_gamma<T>(v0, rc); f[1] = apply_gamma<T>(v1, rc); f[2] = apply_gamma<T>(v2, rc);
+            q[0] = quantise<T>(f[0]); q[1] = quantise<T>(f[1]); q[2] = quantise<T>(f[2]);
+        }
+        return true;
+    };
+    // scoring accumulators of one output pixel; returns its gray byte
+    auto account = [&](const T* f, const int* q) -> int {
+        const int gq = gray_q15(q[0], q[1], q[2]);
+        atomicAdd(&sh_a[0][gq], 1u);
+        atomicAdd(&sh_a[1][hsv_saturation(sm.ct.sdiv, q[0], q[1], q[2])], 1u);
+        lum += (unsigned)lab_L_only(sm.ct.gamma_in, sm.ct.cbrt_tab, q[0], q[1], q[2]);
+        // Hasler-Suesstrunk opponent channels on the FLOAT image, in its own float type
+        const double rg = (double)Ar<T>::sub(f[0], f[1]);
+        const double yb = (double)Ar<T>::sub(Ar<T>::mul((T)0.5, Ar<T>::add(f[0], f[1])), f[2]);
+        m_rg += rg; m_rg2 += rg * rg; m_yb += yb; m_yb2 += yb * yb;
+        return gq;
+    };
+
+    const unsigned p0 = blockIdx.x * (unsigned)a.pix_per_block;
+    const unsigned p1 = min(p0 + (unsigned)a.pix_per_block, npix);
+    const unsigned p1v = words_ok ? p0 + ((p1 - p0) & ~3u) : p0;      // full 4-pixel groups, word I/O
+    for (unsigned p = p0 + 4 * threadIdx.x; p < p1v; p += 4 * NT) {
+        uint32_t w0 = 0, w1 = 0, w2 = 0;
+        float4 f0 = make_float4(0, 0, 0, 0), f1 = f0, f2 = f0;
+        T d[12];
+        if (!dehaze) {
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(frame + (size_t)p * 3);
+            w0 = __ldg(w); w1 = __ldg(w + 1); w2 = __ldg(w + 2);
+        } else if (sizeof(T) == 4 && (reinterpret_cast<uintptr_t>(rec + (size_t)p * 3) & 15) == 0) {
+            const float4* qv = reinterpret_cast<const float4*>(rec + (size_t)p * 3);
+            f0 = qv[0]; f1 = qv[1]; f2 = qv[2];
+            d[0] = (T)f0.x; d[1] = (T)f0.y; d[2] = (T)f0.z; d[3] = (T)f0.w; d[4] = (T)f1.x; d[5] = (T)f1.y;
+            d[6] = (T)f1.z; d[7] = (T)f1.w; d[8] = (T)f2.x; d[9] = (T)f2.y; d[10] = (T)f2.z; d[11] = (T)f2.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 12; ++i) d[i] = rec[(size_t)p * 3 + i];
+        }
+        int y = 0, x = 0;
+        if (clahe) { y = (int)(p / (unsigned)a.W); x = (int)(p - (unsigned)y * (unsigned)a.W); }
+        uint32_t o0 = 0, o1 = 0, o2 = 0, gw = 0;
         T f[3];
         int q[3];
-        if (rc.clahe) {
-            int r, g, bl, L, A, Bc;
-            stage_bytes<T>(a, rc, st, b, s, p, r, g, bl);
-            rgb_to_lab(ct->gamma_in, ct->cbrt_tab, r, g, bl, L, A, Bc);
-            const int y = (int)(p / a.W), x = (int)(p - (size_t)y * a.W);
-            L = clahe_interp(luts, rc.tiles_x, rc.tiles_y, inv_tw, inv_th, y, x, L);
-            int k[3];
-            lab_to_rgb(ct->lab_yf, ct->gamma_out, L, A, Bc, k[0], k[1], k[2]);
-            if (!FINAL) {
-                atomicAdd(&sh_a[0][k[0]], 1u); atomicAdd(&sh_a[1][k[1]], 1u); atomicAdd(&sh_a[2][k[2]], 1u);
-                continue;
-            }
-#pragma unroll
-            for (int c = 0; c < 3; ++c) { f[c] = (T)st.postf[c][k[c]]; q[c] = st.postq[c][k[c]]; }
-        } else if (!rc.dehaze) {
-            const uint8_t* fr = a.frames + ((size_t)b * npix + p) * 3;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) { f[c] = (T)st.postf[c][fr[c]]; q[c] = st.postq[c][fr[c]]; }
-        } else {
-            const int inst = b * a.n_dehaze + a.dehaze_slot[s];
-            const T* x = reinterpret_cast<const T*>(a.recovered) + ((size_t)inst * npix + p) * 3;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                T v = x[c];
-                for (int i = 0; i < rc.n_pre; ++i) v = stretch_apply<T>(v, (T)st.st_lo[i][c], (T)st.st_den[i][c]);
-                v = apply_gamma<T>(v, rc);
-                f[c] = v; q[c] = quantise<T>(v);
-            }
+        // pixel 0: bytes 0..2
+        if (shade(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255, d[0], d[1], d[2], y, x, f, q)) {
+            o0 = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16);
+            gw = (uint32_t)account(f, q);
+        }
+        if (++x == a.W) { x = 0; ++y; }
+        // pixel 1: bytes 3..5
+        if (shade(w0 >> 24, w1 & 255, (w1 >> 8) & 255, d[3], d[4], d[5], y, x, f, q)) {
+            o0 |= (uint32_t)q[0] << 24; o1 = (uint32_t)q[1] | ((uint32_t)q[2] << 8);
+            gw |= (uint32_t)account(f, q) << 8;
+        }
+        if (++x == a.W) { x = 0; ++y; }
+        // pixel 2: bytes 6..8
+        if (shade((w1 >> 16) & 255, w1 >> 24, w2 & 255, d[6], d[7], d[8], y, x, f, q)) {
+            o1 |= ((uint32_t)q[0] << 16) | ((uint32_t)q[1] << 24); o2 = (uint32_t)q[2];
+            gw |= (uint32_t)account(f, q) << 16;
+        }
+        if (++x == a.W) { x = 0; ++y; }
+        // pixel 3: bytes 9..11
+        if (shade((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24, d[9], d[10], d[11], y, x, f, q)) {
+            o2 |= ((uint32_t)q[0] << 8) | ((uint32_t)q[1] << 16) | ((uint32_t)q[2] << 24);
+            gw |= (uint32_t)account(f, q) << 24;
         }
         if (FINAL) {
-            uint8_t* o = out + p * 3;
-            o[0] = (uint8_t)q[0]; o[1] = (uint8_t)q[1]; o[2] = (uint8_t)q[2];
-            const int gq = gray_q15(q[0], q[1], q[2]);
-            gray[p] = (uint8_t)gq;
-            atomicAdd(&sh_a[0][gq], 1u);
-            atomicAdd(&sh_a[1][hsv_saturation(ct->sdiv, q[0], q[1], q[2])], 1u);
-            lum += (unsigned)lab_L_only(ct->gamma_in, ct->cbrt_tab, q[0], q[1], q[2]);
-            // Hasler-Suesstrunk opponent channels on the FLOAT image, in its own float type
-            const double rg = (double)Ar<T>::sub(f[0], f[1]);
-            const double yb = (double)Ar<T>::sub(Ar<T>::mul((T)0.5, Ar<T>::add(f[0], f[1])), f[2]);
-            m_rg += rg; m_rg2 += rg * rg; m_yb += yb; m_yb2 += yb * yb;
+            uint32_t* o = reinterpret_cast<uint32_t*>(out + (size_t)p * 3);
+            o[0] = o0; o[1] = o1; o[2] = o2;
+            *reinterpret_cast<uint32_t*>(gray + p) = gw;
+        }
+    }
+    // what is left: the last 1-3 pixels of the frame, or everything when the buffers are not word-aligned
+    for (unsigned p = p1v + threadIdx.x; p < p1; p += NT) {
+        const uint8_t* fp = frame + (size_t)p * 3;
+        T f[3], d0 = 0, d1 = 0, d2 = 0;
+        int q[3];
+        if (dehaze) { d0 = rec[(size_t)p * 3]; d1 = rec[(size_t)p * 3 + 1]; d2 = rec[(size_t)p * 3 + 2]; }
+        const int y = (int)(p / (unsigned)a.W), x = (int)(p - (unsigned)y * (unsigned)a.W);
+        if (shade(fp[0], fp[1], fp[2], d0, d1, d2, y, x, f, q)) {
+            out[(size_t)p * 3] = (uint8_t)q[0]; out[(size_t)p * 3 + 1] = (uint8_t)q[1]; out[(size_t)p * 3 + 2] = (uint8_t)q[2];
+            gray[p] = (uint8_t)account(f, q);
         }
     }
     __syncthreads();

@@ -222,7 +222,7 @@ int init_engine_shape(uwie_engine* e, const uwie_library* lib, const uwie_strate
         }
     }
     const size_t N = (size_t)H * W;
-    e->pix_per_block = 4096;
+    e->pix_per_block = 8192;     // multiple of 4: apply_kernel moves 4-pixel groups as words
     e->final_blocks = (int)((N + e->pix_per_block - 1) / e->pix_per_block);
     // quadtree: upper bound of the quadrant size per level (ceil halves), enhancement_strategies.py:104-119
     e->quad_dims.clear();
