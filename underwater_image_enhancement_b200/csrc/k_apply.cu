@@ -44,6 +44,9 @@ __device__ __forceinline__ void stage_bytes(const ApplyArgs& a, const Recipe& rc
 }
 
 // ---------------------------------------------------------------- tile histograms -> tile LUTs
+// One block per (tile, strategy, frame).  Tables in shared memory, 4-pixel groups moved as words when the
+// tile lies inside the frame on 4-pixel boundaries (always at the BASELINE sizes); the clip / redistribute /
+// cumulative-sum tail runs on all 256 threads.
 template <class T>
 __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
     const int s = blockIdx.y, b = blockIdx.z;
@@ -53,35 +56,110 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
     const TileGeo geo = tile_geo(a.H, a.W, rc.tiles_x, rc.tiles_y);
     const int tyi = blockIdx.x / rc.tiles_x, txi = blockIdx.x % rc.tiles_x;
     __shared__ unsigned sh[8][256];
+    __shared__ uint16_t s_gamma[256];
+    __shared__ uint16_t s_cbrt[2048 + 8];
+    __shared__ uint8_t s_preq[3][256];
     for (int i = threadIdx.x; i < 8 * 256; i += NT) (&sh[0][0])[i] = 0;
+    for (int i = threadIdx.x; i < 256; i += NT) s_gamma[i] = a.ctab->gamma_in[i];
+    for (int i = threadIdx.x; i < 2048 + 8; i += NT) s_cbrt[i] = a.ctab->cbrt_tab[i];
+    for (int i = threadIdx.x; i < 768; i += NT) (&s_preq[0][0])[i] = (&st.preq[0][0])[i];
+    const bool dehaze = rc.dehaze != 0;
+    const int n_pre = rc.n_pre;
+    T lo[kMaxStretch][3], den[kMaxStretch][3];
+#pragma unroll
+    for (int i = 0; i < kMaxStretch; ++i)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { lo[i][c] = (T)st.st_lo[i][c]; den[i][c] = (T)st.st_den[i][c]; }
     __syncthreads();
     unsigned* h = sh[threadIdx.x >> 5];
+    const size_t npix = (size_t)a.H * a.W;
+    const uint8_t* frame = a.frames + (size_t)b * npix * 3;
+    const T* rec = dehaze ? reinterpret_cast<const T*>(a.recovered) + (size_t)(b * a.n_dehaze + a.dehaze_slot[s]) * npix * 3 : nullptr;
+    auto count_bytes = [&](int r8, int g8, int b8) {
+        atomicAdd(&h[lab_L_only(s_gamma, s_cbrt, s_preq[0][r8], s_preq[1][g8], s_preq[2][b8])], 1u);
+    };
+    auto count_floats = [&](T v0, T v1, T v2) {
+        if (n_pre > 0) {
+            v0 = stretch_apply<T>(v0, lo[0][0], den[0][0]); v1 = stretch_apply<T>(v1, lo[0][1], den[0][1]);
+            v2 = stretch_apply<T>(v2, lo[0][2], den[0][2]);
+        }
+        if (n_pre > 1) {
+            v0 = stretch_apply<T>(v0, lo[1][0], den[1][0]); v1 = stretch_apply<T>(v1, lo[1][1], den[1][1]);
+            v2 = stretch_apply<T>(v2, lo[1][2], den[1][2]);
+        }
+        atomicAdd(&h[lab_L_only(s_gamma, s_cbrt, quantise<T>(v0), quantise<T>(v1), quantise<T>(v2))], 1u);
+    };
     const int area = geo.tw * geo.th;
-    for (int i = threadIdx.x; i < area; i += NT) {
-        const int ly = i / geo.tw, lx = i - ly * geo.tw;
-        int y = tyi * geo.th + ly, x = txi * geo.tw + lx;
-        if (y >= a.H) y = reflect101(y, a.H);
-        if (x >= a.W) x = reflect101(x, a.W);
-        int r, g, bl;
-        stage_bytes<T>(a, rc, st, b, s, (size_t)y * a.W + x, r, g, bl);
-        atomicAdd(&h[lab_L_only(a.ctab->gamma_in, a.ctab->cbrt_tab, r, g, bl)], 1u);
+    const int y0 = tyi * geo.th, x0 = txi * geo.tw;
+    const bool inside = y0 + geo.th <= a.H && x0 + geo.tw <= a.W && (geo.tw & 3) == 0 && (a.W & 3) == 0 &&
+                        (reinterpret_cast<uintptr_t>(frame) & 3) == 0 &&
+                        (!dehaze || (sizeof(T) == 4 && (reinterpret_cast<uintptr_t>(rec) & 15) == 0 && (npix & 3) == 0));
+    if (inside) {
+        const int gpr = geo.tw >> 2;                       // 4-pixel groups per tile row
+        const int groups = gpr * geo.th;
+        for (int i = threadIdx.x; i < groups; i += NT) {
+            const int ly = i / gpr, gx = i - ly * gpr;
+            const size_t p = (size_t)(y0 + ly) * a.W + x0 + 4 * gx;
+            if (!dehaze) {
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(frame + p * 3);
+                const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+                count_bytes(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255);
+                count_bytes(w0 >> 24, w1 & 255, (w1 >> 8) & 255);
+                count_bytes((w1 >> 16) & 255, w1 >> 24, w2 & 255);
+                count_bytes((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24);
+            } else {
+                const float4* q = reinterpret_cast<const float4*>(rec + p * 3);
+                const float4 f0 = q[0], f1 = q[1], f2 = q[2];
+                count_floats((T)f0.x, (T)f0.y, (T)f0.z); count_floats((T)f0.w, (T)f1.x, (T)f1.y);
+                count_floats((T)f1.z, (T)f1.w, (T)f2.x); count_floats((T)f2.y, (T)f2.z, (T)f2.w);
+            }
+        }
+    } else {
+        for (int i = threadIdx.x; i < area; i += NT) {
+            const int ly = i / geo.tw, lx = i - ly * geo.tw;
+            int y = y0 + ly, x = x0 + lx;
+            if (y >= a.H) y = reflect101(y, a.H);          // cv2 pads the plane with REFLECT_101 up to a tile multiple
+            if (x >= a.W) x = reflect101(x, a.W);
+            const size_t p = (size_t)y * a.W + x;
+            if (!dehaze) count_bytes(frame[p * 3], frame[p * 3 + 1], frame[p * 3 + 2]);
+            else count_floats(rec[p * 3], rec[p * 3 + 1], rec[p * 3 + 2]);
+        }
     }
     __syncthreads();
-    __shared__ int hist[256];
-    {
-        unsigned v = 0;
+    // clip, redistribute (clahe_clip_redistribute, in parallel), cumulative sum, LUT
+    __shared__ int s_scan[NT / 32];
+    __shared__ int s_excess;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    int v = 0;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) v += sh[w][threadIdx.x];
-        hist[threadIdx.x] = (int)v;
-    }
+    for (int k = 0; k < 8; ++k) v += (int)sh[k][t];
+    const int clip = rc.clahe_clip;
+    int over = v > clip ? v - clip : 0;
+    if (v > clip) v = clip;
+    int e = over;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
+    if (lane == 0) s_scan[w] = e;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        clahe_clip_redistribute(hist, rc.clahe_clip);
-        const float scale = clahe_lut_scale(area);
-        uint8_t* lut = a.tile_lut + (((size_t)b * a.S + s) * kMaxTiles + blockIdx.x) * 256;
-        int acc = 0;
-        for (int i = 0; i < 256; ++i) { acc += hist[i]; lut[i] = clahe_lut_entry(acc, scale); }
+    if (t == 0) { int tot = 0; for (int k = 0; k < NT / 32; ++k) tot += s_scan[k]; s_excess = tot; }
+    __syncthreads();
+    const int excess = s_excess;
+    const int batch = excess / 256, residual = excess - batch * 256;
+    v += batch;
+    if (residual != 0) {
+        int step = 256 / residual;
+        if (step < 1) step = 1;
+        if (t % step == 0 && t / step < residual) v += 1;      // h[0], h[step], ... while residual lasts
     }
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+    __syncthreads();
+    if (lane == 31) s_scan[w] = incl;
+    __syncthreads();
+    int base = 0;
+    for (int k = 0; k < w; ++k) base += s_scan[k];
+    a.tile_lut[(((size_t)b * a.S + s) * kMaxTiles + blockIdx.x) * 256 + t] = clahe_lut_entry(base + incl, clahe_lut_scale(area));
 }
 
 __device__ __forceinline__ int clahe_interp(const uint8_t* luts, int tiles_x, int tiles_y, float inv_tw,
