@@ -5,9 +5,10 @@
 // BORDER_REFLECT_101, scale applied as a multiplication by 1/(r*r).
 //
 // Three kernels:
-//   gf_prep_kernel      frame bytes -> packed (R, G, B, gray) word plane and dark-channel plane (float32), per frame
-//   gf_ab_kernel        gray, dark -> box sums of I, p, I*p, I*I -> a, b (float64 planes)
-//   gf_recover_kernel   a, b -> mean_a * I + mean_b -> t -> (img - A)/t + A -> recovered frame
+//   gf_prep_kernel      frame bytes -> one 8-byte record per pixel {R | G<<8 | B<<16 | gray<<24, dark channel
+//                       (float32)}, per frame: the marching kernels fetch both with one 64-bit load
+//   gf_ab_kernel        gray, dark -> box sums of I, p, I*p, I*I -> {a, b} (one float64 pair per pixel)
+//   gf_recover_kernel   {a, b} -> mean_a * I + mean_b -> t -> (img - A)/t + A -> recovered frame
 //                       (+ the first level of the percentile histograms, see k_select.cu)
 //
 // Box sums are O(1) per pixel.  Every WARP marches down its own strip of 160 columns with no
@@ -17,6 +18,9 @@
 // sums of 5 CONSECUTIVE outputs with a sliding window (r + 4 reads for 5 outputs).
 // The first-pass sums are exact whatever the order: I = g/255 is carried as the integers (sum g,
 // sum g*g), and p (a float32, multiple of 2^-27) and g*p are summed in float64 far below 2^53 ulps.
+// The kernels are bound by instruction issue and load latency, not by HBM: rows are addressed as a
+// warp-uniform row pointer plus a 32-bit column, records are fetched whole (64 / 128 bits), and the
+// {a, b} pairs leave straight from the registers that computed them.
 #include "k_arith.cuh"
 #include "k_kernels.h"
 
@@ -29,7 +33,7 @@ constexpr int GSPAN = 32 * GC;        // columns a warp carries, outputs = GSPAN
 constexpr int GWARPS = 8;
 constexpr int GNT = 32 * GWARPS;
 
-// ------------------------------------------------------------------ gray + dark channel planes
+// ------------------------------------------------------------------ gray + dark channel records
 __global__ void __launch_bounds__(256) gf_prep_kernel(GuidedArgs a) {
     const int b = blockIdx.y;
     __shared__ float sdiv[3][256];      // img / (A + guard), float32            SS:170, ES:221
@@ -42,21 +46,21 @@ __global__ void __launch_bounds__(256) gf_prep_kernel(GuidedArgs a) {
         sq[c][v] = ct.curq[c][v];
     }
     __syncthreads();
-    const size_t npix = (size_t)a.H * a.W;
+    const unsigned npix = (unsigned)a.H * a.W;
     const uint8_t* f = a.frames + (size_t)b * npix * 3;
-    unsigned* gp = a.pix_plane + (size_t)b * npix;
-    float* dp = a.dark_plane + (size_t)b * npix;
-    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < npix; i += (size_t)gridDim.x * 256) {
+    uint2* gd = a.gd_plane + (size_t)b * npix;
+    for (unsigned i = blockIdx.x * 256 + threadIdx.x; i < npix; i += gridDim.x * 256) {
         const unsigned r = f[i * 3], g = f[i * 3 + 1], bl = f[i * 3 + 2];
         const unsigned gq = (unsigned)gray_q15(sq[0][r], sq[1][g], sq[2][bl]);
-        gp[i] = r | (g << 8) | (bl << 16) | (gq << 24);      // one aligned word per pixel for the marching kernels
-        dp[i] = fminf(fminf(sdiv[0][r], sdiv[1][g]), sdiv[2][bl]);
+        const float dk = fminf(fminf(sdiv[0][r], sdiv[1][g]), sdiv[2][bl]);
+        gd[i] = make_uint2(r | (g << 8) | (bl << 16) | (gq << 24), __float_as_uint(dk));
     }
 }
 
-__device__ __forceinline__ float transmission0(float omega, int clip_t0, float dark) {
+template <bool CLIP>
+__device__ __forceinline__ float transmission0(float omega, float dark) {
     float t0 = __fsub_rn(1.0f, __fmul_rn(omega, dark));           // 1 - omega * dark, float32
-    if (clip_t0) t0 = t0 < 0.1f ? 0.1f : (t0 > 1.0f ? 1.0f : t0); // SS:174
+    if (CLIP) t0 = t0 < 0.1f ? 0.1f : (t0 > 1.0f ? 1.0f : t0);    // SS:174
     return t0;
 }
 
@@ -69,7 +73,7 @@ __device__ __forceinline__ Strip make_strip(const GuidedArgs& a, int r) {
     s.r = r; s.lo = r / 2; s.hi = r - 1 - s.lo;
     s.outw = GSPAN - r + 1;
     s.warp = threadIdx.x >> 5; s.lane = threadIdx.x & 31;
-    s.xs = (blockIdx.x * GWARPS + s.warp) * s.outw;
+    s.xs = (blockIdx.x * (blockDim.x >> 5) + s.warp) * s.outw;
     s.ys = blockIdx.y * a.rows_per_block;
     s.ye = min(s.ys + a.rows_per_block, a.H);
     s.valid = s.xs < a.W && s.ys < s.ye;
@@ -77,6 +81,7 @@ __device__ __forceinline__ Strip make_strip(const GuidedArgs& a, int r) {
 }
 
 // ------------------------------------------------------------------ a, b
+template <bool CLIP>
 __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
     __shared__ double sP[GWARPS][GSPAN];
     __shared__ double sGP[GWARPS][GSPAN];
@@ -87,13 +92,10 @@ __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
     const Strip s = make_strip(a, rc.radius);
     if (!s.valid) return;                                // warp-uniform
     const float omega = rc.omega;
-    const int clip_t0 = a.lib.clip_t0;
     const double eps = rc.eps;
-    const size_t npix = (size_t)a.H * a.W;
-    const unsigned* pix = a.pix_plane + (size_t)b * npix;
-    const float* dark = a.dark_plane + (size_t)b * npix;
-    double* pa = a.ab + (size_t)inst * 2 * npix;
-    double* pb = pa + npix;
+    const unsigned npix = (unsigned)a.H * a.W;
+    const uint2* gd = a.gd_plane + (size_t)b * npix;
+    double2* pab = a.ab + (size_t)inst * npix;
     const double rr = (double)s.r * (double)s.r;
     const double scale = 1.0 / rr;                       // cv2: sum * (1 / (kw * kh))
     const double scale_i = 1.0 / (255.0 * rr), scale_ii = 1.0 / (65025.0 * rr);
@@ -103,52 +105,59 @@ __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
 #pragma unroll
     for (int j = 0; j < GC; ++j) cx[j] = reflect101(s.xs - s.lo + s.lane + 32 * j, a.W);
     double vp[GC], vgp[GC];
-    unsigned long long vg[GC];
+    unsigned vg[GC], vgg[GC];
 #pragma unroll
-    for (int j = 0; j < GC; ++j) { vp[j] = 0.0; vgp[j] = 0.0; vg[j] = 0ull; }
+    for (int j = 0; j < GC; ++j) { vp[j] = 0.0; vgp[j] = 0.0; vg[j] = 0u; vgg[j] = 0u; }
 
-    // Row loads are software-pipelined: the values of the row that enters (leaves) the window in the
+    // Row loads are software-pipelined: the records of the row that enters (leaves) the window in the
     // NEXT step are requested right after this step's were consumed, so their latency hides behind
     // the shared-memory phase instead of stalling a warp that has nothing else to do.
-    unsigned gE[GC], gL[GC];
-    float dE[GC], dL[GC];
-    auto row_load = [&](int yy, unsigned* g, float* d) {
-        const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+    uint2 E[GC], L[GC];
+    auto row_load = [&](int yy, uint2 (&q)[GC]) {
+        const uint2* rowp = gd + (unsigned)reflect101(yy, a.H) * (unsigned)a.W;     // warp-uniform
 #pragma unroll
-        for (int j = 0; j < GC; ++j) { g[j] = pix[ro + cx[j]] >> 24; d[j] = dark[ro + cx[j]]; }
+        for (int j = 0; j < GC; ++j) q[j] = __ldg(rowp + cx[j]);
     };
-    auto row_acc = [&](const unsigned* gq, const float* d, bool add) {
+    auto row_in = [&](const uint2 (&q)[GC]) {
 #pragma unroll
         for (int j = 0; j < GC; ++j) {
-            const unsigned g = gq[j];
-            const double p = (double)transmission0(omega, clip_t0, d[j]);
-            const unsigned long long q = ((unsigned long long)g << 32) | (unsigned long long)(g * g);
-            if (add) { vp[j] += p; vgp[j] += (double)g * p; vg[j] += q; }
-            else { vp[j] -= p; vgp[j] -= (double)g * p; vg[j] -= q; }
+            const unsigned g = q[j].x >> 24;
+            const double p = (double)transmission0<CLIP>(omega, __uint_as_float(q[j].y));
+            vp[j] += p; vgp[j] += (double)g * p; vg[j] += g; vgg[j] += g * g;
         }
     };
-    auto row_add = [&](int yy) { row_load(yy, gE, dE); row_acc(gE, dE, true); };
-
-    for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) row_add(yy);
-    const int base = s.lane * GC;
-    row_load(s.ys + s.hi, gE, dE);
-    row_load(s.ys - s.lo, gL, dL);
-    for (int yo = s.ys; yo < s.ye; ++yo) {
-        row_acc(gE, dE, true);
-        if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, gE, dE);
+    auto row_out = [&](const uint2 (&q)[GC]) {
 #pragma unroll
         for (int j = 0; j < GC; ++j) {
-            wP[s.lane + 32 * j] = vp[j]; wGP[s.lane + 32 * j] = vgp[j]; wG[s.lane + 32 * j] = vg[j];
+            const unsigned g = q[j].x >> 24;
+            const double p = (double)transmission0<CLIP>(omega, __uint_as_float(q[j].y));
+            vp[j] -= p; vgp[j] -= (double)g * p; vg[j] -= g; vgg[j] -= g * g;
+        }
+    };
+
+    for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) { row_load(yy, E); row_in(E); }
+    const int base = s.lane * GC;
+    const bool mine = base < s.outw;
+    row_load(s.ys + s.hi, E);
+    row_load(s.ys - s.lo, L);
+    for (int yo = s.ys; yo < s.ye; ++yo) {
+        row_in(E);
+        if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, E);
+#pragma unroll
+        for (int j = 0; j < GC; ++j) {
+            wP[s.lane + 32 * j] = vp[j]; wGP[s.lane + 32 * j] = vgp[j];
+            wG[s.lane + 32 * j] = ((unsigned long long)vg[j] << 32) | vgg[j];
         }
         __syncwarp();
-        double ra[GC], rb[GC];
-        if (base < s.outw) {
+        if (mine) {
             double hp = 0.0, hgp = 0.0;
             unsigned long long hg = 0ull;
             for (int i = 0; i < s.r; ++i) { hp += wP[base + i]; hgp += wGP[base + i]; hg += wG[base + i]; }
+            double2* orow = pab + (unsigned)yo * (unsigned)a.W + (unsigned)(s.xs + base);
 #pragma unroll
             for (int j = 0; j < GC; ++j) {
-                if (j > 0 && base + j < s.outw) {
+                const bool live = base + j < s.outw && s.xs + base + j < a.W;
+                if (j > 0 && live) {
                     hp += wP[base + j + s.r - 1] - wP[base + j - 1];
                     hgp += wGP[base + j + s.r - 1] - wGP[base + j - 1];
                     hg += wG[base + j + s.r - 1] - wG[base + j - 1];
@@ -159,44 +168,44 @@ __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
                 const double mIP = hgp * scale_i;
                 const double cov = __dsub_rn(mIP, __dmul_rn(mI, mP));
                 const double var = __dsub_rn(mII, __dmul_rn(mI, mI));
-                ra[j] = __ddiv_rn(cov, __dadd_rn(var, eps));
-                rb[j] = __dsub_rn(mP, __dmul_rn(ra[j], mI));
+                const double ra = __ddiv_rn(cov, __dadd_rn(var, eps));
+                const double rb = __dsub_rn(mP, __dmul_rn(ra, mI));
+                if (live) orow[j] = make_double2(ra, rb);
             }
         }
         __syncwarp();
-        if (base < s.outw) {
-#pragma unroll
-            for (int j = 0; j < GC; ++j) { wP[base + j] = ra[j]; wGP[base + j] = rb[j]; }
-        }
-        __syncwarp();
-        const size_t ro = (size_t)yo * a.W;
-        for (int i = s.lane; i < s.outw; i += 32) {
-            const int x = s.xs + i;
-            if (x < a.W) { pa[ro + x] = wP[i]; pb[ro + x] = wGP[i]; }
-        }
-        __syncwarp();
-        row_acc(gL, dL, false);
-        if (yo + 1 < s.ye) row_load(yo + 1 - s.lo, gL, dL);
+        row_out(L);
+        if (yo + 1 < s.ye) row_load(yo + 1 - s.lo, L);
     }
 }
 
 // ------------------------------------------------------------------ recover
+struct RecoverShared {
+    double sA[GWARPS][GSPAN];           // vertical running sums of a, b
+    double sB[GWARPS][GSPAN];
+    double sMA[GWARPS][GSPAN];          // window means of a, b: written by the lane that owns 5 consecutive
+    double sMB[GWARPS][GSPAN];          // columns, read back column-interleaved for coalesced stores
+    double sI[256];                     // g / 255.0
+    float sdiff[3][256];                // img - A, float32              SS:185, ES:247
+    unsigned shist[3 * kSelBinsA];
+};
 template <class T>
 __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
-    __shared__ double sA[GWARPS][GSPAN];
-    __shared__ double sB[GWARPS][GSPAN];
-    __shared__ double sI[256];                 // g / 255.0
-    __shared__ float sdiff[3][256];            // img - A, float32              SS:185, ES:247
-    __shared__ unsigned shist[3 * kSelBinsA];
+    // dynamic shared memory (57 KB, above the static limit), see RecoverShared
+    extern __shared__ __align__(16) unsigned char gf_smem[];
+    RecoverShared& sm = *reinterpret_cast<RecoverShared*>(gf_smem);
+    double (&sI)[256] = sm.sI;
+    float (&sdiff)[3][256] = sm.sdiff;
+    unsigned (&shist)[3 * kSelBinsA] = sm.shist;
     const int inst = blockIdx.z;
     const int b = inst / a.n_dehaze, k = inst % a.n_dehaze;
     const Recipe& rc = a.recipes[a.dehaze_idx[k]];
     const float l0 = a.light[b * 3], l1 = a.light[b * 3 + 1], l2 = a.light[b * 3 + 2];
     {
         const CastTables& ct = a.cast[b];
-        for (int i = threadIdx.x; i < 3 * kSelBinsA; i += GNT) shist[i] = 0;
-        for (int i = threadIdx.x; i < 256; i += GNT) sI[i] = (double)i / 255.0;
-        for (int i = threadIdx.x; i < 768; i += GNT) {
+        for (int i = threadIdx.x; i < 3 * kSelBinsA; i += blockDim.x) shist[i] = 0;
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) sI[i] = (double)i / 255.0;
+        for (int i = threadIdx.x; i < 768; i += blockDim.x) {
             const int c = i >> 8, v = i & 255;
             sdiff[c][v] = __fsub_rn(ct.curf[c][v], c == 0 ? l0 : (c == 1 ? l1 : l2));
         }
@@ -204,13 +213,13 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
     __syncthreads();
     const Strip s = make_strip(a, rc.radius);
     if (s.valid) {
-        const size_t npix = (size_t)a.H * a.W;
-        const unsigned* pix = a.pix_plane + (size_t)b * npix;
-        const double* pa = a.ab + (size_t)inst * 2 * npix;
-        const double* pb = pa + npix;
+        const unsigned npix = (unsigned)a.H * a.W;
+        const uint2* gd = a.gd_plane + (size_t)b * npix;
+        const double2* pab = a.ab + (size_t)inst * npix;
         T* out = reinterpret_cast<T*>(a.recovered) + (size_t)inst * npix * 3;
         const double scale = 1.0 / ((double)s.r * (double)s.r);
-        double* wA = sA[s.warp]; double* wB = sB[s.warp];
+        double* wA = sm.sA[s.warp]; double* wB = sm.sB[s.warp];
+        double* mA = sm.sMA[s.warp]; double* mB = sm.sMB[s.warp];
         const double dl0 = (double)l0, dl1 = (double)l1, dl2 = (double)l2;
 
         int cx[GC];
@@ -219,38 +228,37 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
         double va[GC], vb[GC];
 #pragma unroll
         for (int j = 0; j < GC; ++j) { va[j] = 0.0; vb[j] = 0.0; }
-        double aE[GC], bE[GC], aL[GC], bL[GC];           // software-pipelined row loads (see gf_ab_kernel)
-        auto row_load = [&](int yy, double* qa, double* qb) {
-            const size_t ro = (size_t)reflect101(yy, a.H) * a.W;
+        // row loads: both are requested right before the long recovery step of a row, the entering
+        // row for the NEXT step and the leaving row for this one (consumed after that step)
+        double2 E[GC], L[GC];
+        auto row_load = [&](int yy, double2 (&q)[GC]) {
+            const double2* rowp = pab + (unsigned)reflect101(yy, a.H) * (unsigned)a.W;   // warp-uniform
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { qa[j] = pa[ro + cx[j]]; qb[j] = pb[ro + cx[j]]; }
+            for (int j = 0; j < GC; ++j) q[j] = __ldg(rowp + cx[j]);
         };
-        auto row_add = [&](int yy) {
-            row_load(yy, aE, bE);
+        for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) {
+            row_load(yy, E);
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] += aE[j]; vb[j] += bE[j]; }
-        };
-        for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) row_add(yy);
+            for (int j = 0; j < GC; ++j) { va[j] += E[j].x; vb[j] += E[j].y; }
+        }
         const int base = s.lane * GC;
-        row_load(s.ys + s.hi, aE, bE);
-        row_load(s.ys - s.lo, aL, bL);
+        const bool mine = base < s.outw;
+        row_load(s.ys + s.hi, E);
         for (int yo = s.ys; yo < s.ye; ++yo) {
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] += aE[j]; vb[j] += bE[j]; }
-            if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, aE, bE);
+            for (int j = 0; j < GC; ++j) { va[j] += E[j].x; vb[j] += E[j].y; }
             // this row's pixels (frame bytes + gray) for the recovery step below, requested early
-            const size_t ro = (size_t)yo * a.W;
+            const unsigned ro = (unsigned)yo * (unsigned)a.W;
             unsigned pixw[GC];
 #pragma unroll
             for (int j = 0; j < GC; ++j) {
                 const int x = s.xs + s.lane + 32 * j;
-                pixw[j] = (s.lane + 32 * j < s.outw && x < a.W) ? pix[ro + x] : 0u;
+                pixw[j] = (s.lane + 32 * j < s.outw && x < a.W) ? __ldg(&gd[ro + x].x) : 0u;
             }
 #pragma unroll
             for (int j = 0; j < GC; ++j) { wA[s.lane + 32 * j] = va[j]; wB[s.lane + 32 * j] = vb[j]; }
             __syncwarp();
-            double ma[GC], mb[GC];
-            if (base < s.outw) {
+            if (mine) {
                 double ha = 0.0, hb = 0.0;
                 for (int i = 0; i < s.r; ++i) { ha += wA[base + i]; hb += wB[base + i]; }
 #pragma unroll
@@ -259,22 +267,19 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
                         ha += wA[base + j + s.r - 1] - wA[base + j - 1];
                         hb += wB[base + j + s.r - 1] - wB[base + j - 1];
                     }
-                    ma[j] = ha * scale; mb[j] = hb * scale;
+                    mA[base + j] = ha * scale; mB[base + j] = hb * scale;
                 }
             }
             __syncwarp();
-            if (base < s.outw) {
-#pragma unroll
-                for (int j = 0; j < GC; ++j) { wA[base + j] = ma[j]; wB[base + j] = mb[j]; }
-            }
-            __syncwarp();
+            if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, E);
+            row_load(yo - s.lo, L);
 #pragma unroll
             for (int jj = 0; jj < GC; ++jj) {
                 const int i = s.lane + 32 * jj;
                 const int x = s.xs + i;
                 if (i >= s.outw || x >= a.W) continue;
                 const int r0 = pixw[jj] & 255, g0 = (pixw[jj] >> 8) & 255, b0 = (pixw[jj] >> 16) & 255;
-                double t = __dadd_rn(__dmul_rn(wA[i], sI[pixw[jj] >> 24]), wB[i]);
+                double t = __dadd_rn(__dmul_rn(mA[i], sI[pixw[jj] >> 24]), mB[i]);
                 t = t < 0.1 ? 0.1 : (t > 1.0 ? 1.0 : t);
                 // (img - A) in float32, / t and + A in float64, stored in the library's float type
                 double q0, q1, q2;
@@ -293,7 +298,7 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
                 const T v0 = clip01<T>((T)__dadd_rn(q0, dl0));
                 const T v1 = clip01<T>((T)__dadd_rn(q1, dl1));
                 const T v2 = clip01<T>((T)__dadd_rn(q2, dl2));
-                T* o = out + (ro + x) * 3;
+                T* o = out + (size_t)(ro + x) * 3;
                 o[0] = v0; o[1] = v1; o[2] = v2;
                 atomicAdd(&shist[0 * kSelBinsA + sel_bin_a<T>(v0)], 1u);
                 atomicAdd(&shist[1 * kSelBinsA + sel_bin_a<T>(v1)], 1u);
@@ -301,13 +306,12 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
             }
             __syncwarp();
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] -= aL[j]; vb[j] -= bL[j]; }
-            if (yo + 1 < s.ye) row_load(yo + 1 - s.lo, aL, bL);
+            for (int j = 0; j < GC; ++j) { va[j] -= L[j].x; vb[j] -= L[j].y; }
         }
     }
     __syncthreads();
     unsigned* gh = a.sel_hist_a + (size_t)inst * 3 * kSelBinsA;
-    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += GNT) {
+    for (int i = threadIdx.x; i < 3 * kSelBinsA; i += blockDim.x) {
         const unsigned v = shist[i];
         if (v) atomicAdd(&gh[i], v);
     }
@@ -324,13 +328,22 @@ int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st) {
     gf_prep_kernel<<<dim3(pb, a.B), 256, 0, st>>>(a);
     const int chunks = (a.H + a.rows_per_block - 1) / a.rows_per_block;
     // strips are sized by each instance's own radius; the grid covers the largest radius present
-    // (fewest outputs per strip); for a smaller radius the surplus warps exit at once
+    // (fewest outputs per strip); for a smaller radius the surplus warps exit at once.
+    // Warps per block: the strips spread evenly over the fewest blocks (1920 columns: 14 strips = 2 x 7 warps)
     const int outw_min = GSPAN - max_radius + 1;
     const int strips = (a.W + outw_min - 1) / outw_min;
-    dim3 grid((strips + GWARPS - 1) / GWARPS, chunks, inst);
-    gf_ab_kernel<<<grid, GNT, 0, st>>>(a);
-    if (a.lib.f64) gf_recover_kernel<double><<<grid, GNT, 0, st>>>(a);
-    else gf_recover_kernel<float><<<grid, GNT, 0, st>>>(a);
+    const int bx = (strips + GWARPS - 1) / GWARPS;
+    const int nt = 32 * ((strips + bx - 1) / bx);
+    dim3 grid(bx, chunks, inst);
+    if (a.lib.clip_t0) gf_ab_kernel<true><<<grid, nt, 0, st>>>(a);
+    else gf_ab_kernel<false><<<grid, nt, 0, st>>>(a);
+    static const bool optin = [] {
+        return cudaFuncSetAttribute(gf_recover_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RecoverShared)) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_recover_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RecoverShared)) == cudaSuccess;
+    }();
+    (void)optin;                                        // a failure shows up as a launch error below
+    if (a.lib.f64) gf_recover_kernel<double><<<grid, nt, sizeof(RecoverShared), st>>>(a);
+    else gf_recover_kernel<float><<<grid, nt, sizeof(RecoverShared), st>>>(a);
     return 3;
 }
 

@@ -90,12 +90,12 @@ struct GuidedArgs {
     int n_dehaze;                // number of dehaze strategies
     int dehaze_idx[kStrategiesMax];   // their strategy indices
     int rows_per_block;
-    unsigned* pix_plane;         // [B][H][W]   R | G << 8 | B << 16 | gray << 24 of the (colour-corrected) frame
-    float* dark_plane;           // [B][H][W]   min_c img / (A + guard)
+    uint2* gd_plane;             // [B][H][W]   {R | G << 8 | B << 16 | gray << 24 of the (colour-corrected) frame,
+                                 //              float32 bits of min_c img / (A + guard)}
     const uint8_t* frames;
     const CastTables* cast;
     const float* light;          // [B][3]
-    double* ab;                  // [B * n_dehaze][2][H][W]
+    double2* ab;                 // [B * n_dehaze][H][W] {a, b}
     void* recovered;             // [B * n_dehaze][H][W][3] in the library's float type
     unsigned* sel_hist_a;        // [B * n_dehaze][3][kSelBinsA]
 };

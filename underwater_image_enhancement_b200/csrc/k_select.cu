@@ -133,7 +133,20 @@ __device__ __forceinline__ void agg_add(unsigned* h, unsigned bin, unsigned hits
 }
 
 // ---- level B / C: one streaming read of the recovered frame of an instance
-template <class T, int LEVEL>
+// 12 consecutive values (4 pixels) with 16-byte loads
+__device__ __forceinline__ void load12(const float* p, float (&v)[12]) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { const float4 f = __ldg(q + i); v[4 * i] = f.x; v[4 * i + 1] = f.y; v[4 * i + 2] = f.z; v[4 * i + 3] = f.w; }
+}
+__device__ __forceinline__ void load12(const double* p, double (&v)[12]) {
+    const double2* q = reinterpret_cast<const double2*>(p);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) { const double2 f = __ldg(q + i); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+}
+
+// VEC: every thread takes 4 pixels per round (n % 4 == 0, so every instance starts 16-byte aligned)
+template <class T, int LEVEL, bool VEC>
 __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
     __shared__ PassState ps;
     const int inst = blockIdx.y;
@@ -142,27 +155,41 @@ __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
     constexpr unsigned SUBMASK = LEVEL == 1 ? 2047u : 1023u;
     constexpr int SUBSHIFT = LEVEL == 1 ? 10 : 0;
     constexpr int BINS = LEVEL == 1 ? kSelBinsB : kSelBinsC;
+    constexpr int PER = VEC ? 4 : 1;                            // pixels per thread and round
     const T* src = reinterpret_cast<const T*>(a.recovered) + (size_t)inst * a.n * 3;
     unsigned* gh = (LEVEL == 1 ? a.sel_hist_b : a.sel_hist_c) + (size_t)inst * kSelTargets * BINS;
+    const long long units = a.n / PER;
     const long long stride = (long long)gridDim.x * NT;
-    const long long rounds = (a.n + stride - 1) / stride;       // whole warps stay in the loop
+    const long long rounds = (units + stride - 1) / stride;     // whole warps stay in the loop
     for (long long rd = 0; rd < rounds; ++rd) {
-        const long long px = rd * stride + (long long)blockIdx.x * NT + threadIdx.x;
-        const bool in = px < a.n;
-        unsigned key[3];
-        bool hot = false;
+        const long long u = rd * stride + (long long)blockIdx.x * NT + threadIdx.x;
+        const bool in = u < units;
+        T x[3 * PER];
+        if (VEC) {
+            if (in) load12(src + u * 12, reinterpret_cast<T(&)[12]>(x));
+            else {
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            const T x = in ? src[px * 3 + c] : (T)0;
-            key[c] = x != (T)0 ? sel_key<T>(x) : 0xffffffffu;   // exact zeros live in level-A bin 0, not here
-            hot |= (key[c] >> 21) <= 1024u ? ps.hot[c][key[c] >> 21] != 0 : false;
+                for (int j = 0; j < 3 * PER; ++j) x[j] = (T)0;
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) x[c] = in ? src[u * 3 + c] : (T)0;
         }
-        if (__ballot_sync(0xffffffffu, hot) == 0) continue;     // the common case
+        unsigned key[3 * PER];
+        unsigned hot = 0;
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            const bool hc = (key[c] >> 21) <= 1024u ? ps.hot[c][key[c] >> 21] != 0 : false;
+        for (int j = 0; j < 3 * PER; ++j) {
+            key[j] = x[j] != (T)0 ? sel_key<T>(x[j]) : 0xffffffffu;   // exact zeros live in level-A bin 0, not here
+            const unsigned ka = key[j] >> 21;
+            if (ka <= 1024u && ps.hot[j % 3][ka] != 0) hot |= 1u << j;
+        }
+        if (__ballot_sync(0xffffffffu, hot != 0) == 0) continue;     // the common case
+#pragma unroll
+        for (int j = 0; j < 3 * PER; ++j) {
+            const int c = j % 3;
+            const bool hc = (hot >> j) & 1u;
             if (__ballot_sync(0xffffffffu, hc) == 0) continue;
-            const unsigned hi = key[c] >> SHIFT, sub = (key[c] >> SUBSHIFT) & SUBMASK;
+            const unsigned hi = key[j] >> SHIFT, sub = (key[j] >> SUBSHIFT) & SUBMASK;
             for (int t = 0; t < 8; ++t) {
                 const int tg = c * 8 + t;
                 if (!ps.on[tg]) continue;                        // uniform
@@ -302,9 +329,14 @@ template <class T>
 int launch_select_t(const SelectArgs& a, int inst, int nblk, cudaStream_t st) {
     int launches = 0;
     sel_scan_kernel<0><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
-    sel_hist_kernel<T, 1><<<dim3(nblk, inst), NT, 0, st>>>(a); ++launches;
+    const bool vec = a.n % 4 == 0 && reinterpret_cast<uintptr_t>(a.recovered) % 16 == 0;
+    if (vec) sel_hist_kernel<T, 1, true><<<dim3(nblk, inst), NT, 0, st>>>(a);
+    else sel_hist_kernel<T, 1, false><<<dim3(nblk, inst), NT, 0, st>>>(a);
+    ++launches;
     sel_scan_kernel<1><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
-    sel_hist_kernel<T, 2><<<dim3(nblk, inst), NT, 0, st>>>(a); ++launches;
+    if (vec) sel_hist_kernel<T, 2, true><<<dim3(nblk, inst), NT, 0, st>>>(a);
+    else sel_hist_kernel<T, 2, false><<<dim3(nblk, inst), NT, 0, st>>>(a);
+    ++launches;
     sel_scan_kernel<2><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
     sel_table_kernel<T><<<dim3(nblk, inst), NT, 0, st>>>(a); ++launches;
     sel_finish_kernel<T><<<inst, NT, 0, st>>>(a); ++launches;

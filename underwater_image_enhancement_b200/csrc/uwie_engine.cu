@@ -190,8 +190,7 @@ void plan_layout(uwie_engine* e) {
     L.ab = b.take(B * nd * 2 * N * 8);
     L.recovered = b.take(B * nd * N * 3 * tsz);
     L.targets = b.take(B * nd * kSelTargets * sizeof(SelTarget));
-    L.gf_gray = b.take(nd ? B * N * 4 : 0);
-    L.gf_dark = b.take(nd ? B * N * 4 : 0);
+    L.gf_gray = b.take(nd ? B * N * 8 : 0);
     L.tile_lut = b.take(e->max_tiles ? B * S * kMaxTiles * 256 : 0);
     L.out = b.take(B * S * N * 3);
     L.gray = b.take(B * S * N);
@@ -453,14 +452,20 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         ga.n_dehaze = e->n_dehaze;
         for (int i = 0; i < kStrategiesMax; ++i) ga.dehaze_idx[i] = e->dehaze_idx[i];
         {
-            // row chunks: more chunks = more warps in flight, but each chunk re-reads r - 1 warm-up rows
-            int chunks = H >= 512 ? 12 : (H >= 128 ? 2 : 1);
-            if (const char* ev = std::getenv("UWIE_GF_CHUNKS")) { const int v = std::atoi(ev); if (v >= 1 && v <= H) chunks = v; }
+            // row chunks: every chunk re-reads r - 1 warm-up rows, so as few as fill the machine ONCE
+            // (2 blocks per SM; all blocks do the same work, a second partial wave would only be a tail)
+            const int outw_min = 160 - e->max_radius + 1;
+            const int strips = (W + outw_min - 1) / outw_min;
+            const int per_chunk = ((strips + 7) / 8) * batch * e->n_dehaze;
+            int chunks = (148 * 2) / (per_chunk > 0 ? per_chunk : 1);
+            const int most = H / (3 * (e->max_radius > 0 ? e->max_radius : 1));
+            if (chunks > most) chunks = most;
+            if (chunks < 1) chunks = 1;
             ga.rows_per_block = (H + chunks - 1) / chunks;
         }
-        ga.pix_plane = e->at<unsigned>(L.gf_gray); ga.dark_plane = e->at<float>(L.gf_dark);
+        ga.gd_plane = e->at<uint2>(L.gf_gray);
         ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;
-        ga.ab = e->at<double>(L.ab); ga.recovered = e->at<void>(L.recovered);
+        ga.ab = e->at<double2>(L.ab); ga.recovered = e->at<void>(L.recovered);
         ga.sel_hist_a = e->at<unsigned>(L.sel_hist_a);
         stage(e, st, "guided_recover", launches);
         launches += launch_guided(ga, e->max_radius, st);
