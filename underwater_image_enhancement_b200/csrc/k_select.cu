@@ -108,6 +108,8 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
 struct PassState {
     unsigned pre[kSelTargets];
     int on[kSelTargets];
+    int list[3][8];              // per channel: the targets that are on, compacted
+    int cnt[3];
     uint8_t hot[3][kSelBinsA];
 };
 template <int LEVEL>      // 1, 2: prefixes hold 11 / 22 bits; 3: all 32
@@ -123,7 +125,14 @@ __device__ __forceinline__ bool pass_prologue(const SelectArgs& a, int inst, Pas
         ps.on[threadIdx.x] = on;
         if (on) ps.hot[threadIdx.x >> 3][LEVEL == 1 ? t.prefix : (LEVEL == 2 ? t.prefix >> 11 : t.prefix >> 21)] = 1;
     }
-    return __syncthreads_or(threadIdx.x < kSelTargets && ps.on[threadIdx.x]) != 0;
+    const bool any = __syncthreads_or(threadIdx.x < kSelTargets && ps.on[threadIdx.x]) != 0;
+    if (threadIdx.x < 3) {
+        int n = 0;
+        for (int t = 0; t < 8; ++t) if (ps.on[threadIdx.x * 8 + t]) ps.list[threadIdx.x][n++] = threadIdx.x * 8 + t;
+        ps.cnt[threadIdx.x] = n;
+    }
+    __syncthreads();
+    return any;
 }
 
 // warp-aggregated histogram increment for the lanes in `hits` (all of them call this)
@@ -190,9 +199,10 @@ __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
             const bool hc = (hot >> j) & 1u;
             if (__ballot_sync(0xffffffffu, hc) == 0) continue;
             const unsigned hi = key[j] >> SHIFT, sub = (key[j] >> SUBSHIFT) & SUBMASK;
-            for (int t = 0; t < 8; ++t) {
-                const int tg = c * 8 + t;
-                if (!ps.on[tg]) continue;                        // uniform
+            const int nt = ps.cnt[c];                            // uniform
+#pragma unroll 1
+            for (int t = 0; t < nt; ++t) {
+                const int tg = ps.list[c][t];
                 const bool hit = hc && ps.pre[tg] == hi;
                 const unsigned hits = __ballot_sync(0xffffffffu, hit);
                 if (hit) agg_add(gh + (size_t)tg * BINS, sub, hits);
@@ -242,9 +252,10 @@ __global__ void __launch_bounds__(NT) sel_table_kernel(SelectArgs a) {
             const bool hc = (key[c] >> 21) <= 1024u ? ps.hot[c][key[c] >> 21] != 0 : false;
             if (__ballot_sync(0xffffffffu, hc) == 0) continue;
             const unsigned long long bits = sel_bits<T>(x[c]);
-            for (int t = 0; t < 8; ++t) {
-                const int tg = c * 8 + t;
-                if (!ps.on[tg]) continue;
+            const int nt = ps.cnt[c];                            // uniform
+#pragma unroll 1
+            for (int t = 0; t < nt; ++t) {
+                const int tg = ps.list[c][t];
                 const bool hit = hc && ps.pre[tg] == key[c];
                 const unsigned hits = __ballot_sync(0xffffffffu, hit);
                 if (hit) {
@@ -326,7 +337,21 @@ __global__ void __launch_bounds__(NT) sel_finish_kernel(SelectArgs a) {
 }
 
 template <class T>
-int launch_select_t(const SelectArgs& a, int inst, int nblk, cudaStream_t st) {
+int launch_select_t(const SelectArgs& a, int inst, cudaStream_t st) {
+    // ONE wave of blocks across all instances: every block does the same number of rounds, so a second
+    // partial wave would only be a tail.  Resident blocks per SM come from the occupancy calculator.
+    static const int resident = [] {
+        int b1 = 0, b2 = 0, sms = 0, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, sel_hist_kernel<T, 1, true>, NT, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, sel_hist_kernel<T, 2, true>, NT, 0);
+        const int b = b1 < b2 ? b1 : b2;
+        return (b > 0 ? b : 4) * (sms > 0 ? sms : 148);
+    }();
+    const long long per = (a.n + NT * 8 - 1) / (NT * 8);
+    const int cap = resident / inst < 1 ? 1 : resident / inst;
+    const int nblk = (int)(per < 1 ? 1 : (per > cap ? cap : per));
     int launches = 0;
     sel_scan_kernel<0><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
     const bool vec = a.n % 4 == 0 && reinterpret_cast<uintptr_t>(a.recovered) % 16 == 0;
@@ -348,12 +373,7 @@ int launch_select_t(const SelectArgs& a, int inst, int nblk, cudaStream_t st) {
 int launch_select(const SelectArgs& a, cudaStream_t st) {
     if (a.n_dehaze == 0) return 0;
     const int inst = a.B * a.n_dehaze;
-    // enough blocks to fill the machine across all instances, few enough that the per-block prologue
-    // (3 KB of flags) stays negligible
-    long long per = (a.n + NT * 8 - 1) / (NT * 8);
-    const int cap = (148 * 8 + inst - 1) / inst < 4 ? 4 : (148 * 8 + inst - 1) / inst;
-    const int nblk = (int)(per < 1 ? 1 : (per > cap ? cap : per));
-    return a.lib.f64 ? launch_select_t<double>(a, inst, nblk, st) : launch_select_t<float>(a, inst, nblk, st);
+    return a.lib.f64 ? launch_select_t<double>(a, inst, st) : launch_select_t<float>(a, inst, st);
 }
 
 }  // namespace uwie
