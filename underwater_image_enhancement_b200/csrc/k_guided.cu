@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
     for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) { row_load(yy, E); row_in(E); }
     const int base = s.lane * GC;
     const bool mine = base < s.outw;
+    const int nblocks = s.r / GC;
     row_load(s.ys + s.hi, E);
     row_load(s.ys - s.lo, L);
     for (int yo = s.ys; yo < s.ye; ++yo) {
@@ -149,10 +150,24 @@ __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
             wG[s.lane + 32 * j] = ((unsigned long long)vg[j] << 32) | vgg[j];
         }
         __syncwarp();
+        // window of the first output of a lane = r / 5 whole 5-column blocks (its own and its right-hand
+        // neighbours', fetched by shuffle) + r % 5 single columns; the sums are exact in any order
+        double hp = 0.0, hgp = 0.0;
+        unsigned long long hg = 0ull;
+        {
+            double bp = 0.0, bgp = 0.0;
+            unsigned long long bg = 0ull;
+#pragma unroll
+            for (int j = 0; j < GC; ++j) { bp += wP[base + j]; bgp += wGP[base + j]; bg += wG[base + j]; }
+            if (nblocks > 0) { hp = bp; hgp = bgp; hg = bg; }
+            for (int t = 1; t < nblocks; ++t) {                   // warp-uniform trip count
+                hp += __shfl_down_sync(0xffffffffu, bp, t);
+                hgp += __shfl_down_sync(0xffffffffu, bgp, t);
+                hg += __shfl_down_sync(0xffffffffu, bg, t);
+            }
+        }
         if (mine) {
-            double hp = 0.0, hgp = 0.0;
-            unsigned long long hg = 0ull;
-            for (int i = 0; i < s.r; ++i) { hp += wP[base + i]; hgp += wGP[base + i]; hg += wG[base + i]; }
+            for (int i = nblocks * GC; i < s.r; ++i) { hp += wP[base + i]; hgp += wGP[base + i]; hg += wG[base + i]; }
             double2* orow = pab + (unsigned)yo * (unsigned)a.W + (unsigned)(s.xs + base);
 #pragma unroll
             for (int j = 0; j < GC; ++j) {
@@ -243,6 +258,7 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
         }
         const int base = s.lane * GC;
         const bool mine = base < s.outw;
+        const int nblocks = s.r / GC;
         row_load(s.ys + s.hi, E);
         for (int yo = s.ys; yo < s.ye; ++yo) {
 #pragma unroll
@@ -258,9 +274,19 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
 #pragma unroll
             for (int j = 0; j < GC; ++j) { wA[s.lane + 32 * j] = va[j]; wB[s.lane + 32 * j] = vb[j]; }
             __syncwarp();
+            double ha = 0.0, hb = 0.0;                     // first window by blocks, see gf_ab_kernel
+            {
+                double ba = 0.0, bb = 0.0;
+#pragma unroll
+                for (int j = 0; j < GC; ++j) { ba += wA[base + j]; bb += wB[base + j]; }
+                if (nblocks > 0) { ha = ba; hb = bb; }
+                for (int t = 1; t < nblocks; ++t) {
+                    ha += __shfl_down_sync(0xffffffffu, ba, t);
+                    hb += __shfl_down_sync(0xffffffffu, bb, t);
+                }
+            }
             if (mine) {
-                double ha = 0.0, hb = 0.0;
-                for (int i = 0; i < s.r; ++i) { ha += wA[base + i]; hb += wB[base + i]; }
+                for (int i = nblocks * GC; i < s.r; ++i) { ha += wA[base + i]; hb += wB[base + i]; }
 #pragma unroll
                 for (int j = 0; j < GC; ++j) {
                     if (j > 0 && base + j < s.outw) {
