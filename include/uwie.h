@@ -188,6 +188,14 @@ size_t uwie_features79_workspace_bytes(int batch, int height, int width);
 int uwie_features79(const uint8_t* frames_dev, int batch, int height, int width, double* feat_dev,
                     void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Self-test of the guided filter's branch-free float64 division and reciprocal (k_arith.cuh) against the
+ * compiler's IEEE-754 routines: `count` seeded operand pairs in the ranges the kernels guarantee
+ * (divisor in [1e-9, 2], dividend 0 or |x| in [1e-18, 2]; reciprocal of t in [0.1, 1]).
+ * *mismatches_host receives the number of results whose bits differ (must be 0).  Synchronous.
+ * ------------------------------------------------------------------------------------------- */
+int uwie_selftest_division(unsigned long long count, unsigned long long seed, unsigned long long* mismatches_host);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,7 +19,7 @@ EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_byt
            "uwie_engine_last_launches", "uwie_engine_debug", "uwie_engine_profile",
            "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_features_u8",
            "uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32", "uwie_features79_workspace_bytes",
-           "uwie_features79", "uwie_quality_workspace_bytes", "uwie_quality_scores")
+           "uwie_features79", "uwie_quality_workspace_bytes", "uwie_quality_scores", "uwie_selftest_division")
 FEATURES = 79
 VGG_FEATURES = 79
 STAGE_NAME_LEN = 32
@@ -106,6 +106,8 @@ def load() -> C.CDLL:
     lib.uwie_quality_scores.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_void_p,
                                         C.c_void_p, C.c_size_t, C.c_void_p]
     lib.uwie_quality_scores.restype = C.c_int
+    lib.uwie_selftest_division.argtypes = [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong)]
+    lib.uwie_selftest_division.restype = C.c_int
     _lib = lib
     return lib
 

@@ -81,7 +81,7 @@ __device__ __forceinline__ Strip make_strip(const GuidedArgs& a, int r) {
 }
 
 // ------------------------------------------------------------------ a, b
-template <bool CLIP>
+template <bool CLIP, bool FAST>
 __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
     __shared__ double sP[GWARPS][GSPAN];
     __shared__ double sGP[GWARPS][GSPAN];
@@ -137,7 +137,6 @@ __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
 
     for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) { row_load(yy, E); row_in(E); }
     const int base = s.lane * GC;
-    const bool mine = base < s.outw;
     const int nblocks = s.r / GC;
     row_load(s.ys + s.hi, E);
     row_load(s.ys - s.lo, L);
@@ -166,27 +165,32 @@ __global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
                 hg += __shfl_down_sync(0xffffffffu, bg, t);
             }
         }
-        if (mine) {
-            for (int i = nblocks * GC; i < s.r; ++i) { hp += wP[base + i]; hgp += wGP[base + i]; hg += wG[base + i]; }
-            double2* orow = pab + (unsigned)yo * (unsigned)a.W + (unsigned)(s.xs + base);
+        // Every lane forms all 5 outputs in straight-line code (dead ones from clamped reads) so that the
+        // five dependent chains of a / b interleave; only the stores are predicated.
+        for (int i = nblocks * GC; i < s.r; ++i) {
+            const int c = min(base + i, GSPAN - 1);
+            hp += wP[c]; hgp += wGP[c]; hg += wG[c];
+        }
+        double2* orow = pab + (unsigned)yo * (unsigned)a.W + (unsigned)(s.xs + base);
 #pragma unroll
-            for (int j = 0; j < GC; ++j) {
-                const bool live = base + j < s.outw && s.xs + base + j < a.W;
-                if (j > 0 && live) {
-                    hp += wP[base + j + s.r - 1] - wP[base + j - 1];
-                    hgp += wGP[base + j + s.r - 1] - wGP[base + j - 1];
-                    hg += wG[base + j + s.r - 1] - wG[base + j - 1];
-                }
-                const double mI = (double)(unsigned)(hg >> 32) * scale_i;
-                const double mII = (double)(unsigned)(hg & 0xffffffffull) * scale_ii;
-                const double mP = hp * scale;
-                const double mIP = hgp * scale_i;
-                const double cov = __dsub_rn(mIP, __dmul_rn(mI, mP));
-                const double var = __dsub_rn(mII, __dmul_rn(mI, mI));
-                const double ra = __ddiv_rn(cov, __dadd_rn(var, eps));
-                const double rb = __dsub_rn(mP, __dmul_rn(ra, mI));
-                if (live) orow[j] = make_double2(ra, rb);
+        for (int j = 0; j < GC; ++j) {
+            if (j > 0) {
+                const int in = min(base + j + s.r - 1, GSPAN - 1);
+                hp += wP[in] - wP[base + j - 1];
+                hgp += wGP[in] - wGP[base + j - 1];
+                hg += wG[in] - wG[base + j - 1];
             }
+            const double mI = (double)(unsigned)(hg >> 32) * scale_i;
+            const double mII = (double)(unsigned)(hg & 0xffffffffull) * scale_ii;
+            const double mP = hp * scale;
+            const double mIP = hgp * scale_i;
+            const double cov = __dsub_rn(mIP, __dmul_rn(mI, mP));
+            const double var = __dsub_rn(mII, __dmul_rn(mI, mI));
+            const double den = __dadd_rn(var, eps);
+            // FAST: eps >= 1e-9, so den is normal and |a| < 1e10 (a is 0 or far above the subnormals)
+            const double ra = FAST ? div_rn_normal(cov, den) : __ddiv_rn(cov, den);
+            const double rb = __dsub_rn(mP, __dmul_rn(ra, mI));
+            if (base + j < s.outw && s.xs + base + j < a.W) orow[j] = make_double2(ra, rb);
         }
         __syncwarp();
         row_out(L);
@@ -257,7 +261,6 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
             for (int j = 0; j < GC; ++j) { va[j] += E[j].x; vb[j] += E[j].y; }
         }
         const int base = s.lane * GC;
-        const bool mine = base < s.outw;
         const int nblocks = s.r / GC;
         row_load(s.ys + s.hi, E);
         for (int yo = s.ys; yo < s.ye; ++yo) {
@@ -285,38 +288,42 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
                     hb += __shfl_down_sync(0xffffffffu, bb, t);
                 }
             }
-            if (mine) {
-                for (int i = nblocks * GC; i < s.r; ++i) { ha += wA[base + i]; hb += wB[base + i]; }
+            for (int i = nblocks * GC; i < s.r; ++i) {
+                const int c = min(base + i, GSPAN - 1);
+                ha += wA[c]; hb += wB[c];
+            }
 #pragma unroll
-                for (int j = 0; j < GC; ++j) {
-                    if (j > 0 && base + j < s.outw) {
-                        ha += wA[base + j + s.r - 1] - wA[base + j - 1];
-                        hb += wB[base + j + s.r - 1] - wB[base + j - 1];
-                    }
-                    mA[base + j] = ha * scale; mB[base + j] = hb * scale;
+            for (int j = 0; j < GC; ++j) {                  // all lanes, dead outputs from clamped reads
+                if (j > 0) {
+                    const int in = min(base + j + s.r - 1, GSPAN - 1);
+                    ha += wA[in] - wA[base + j - 1];
+                    hb += wB[in] - wB[base + j - 1];
                 }
+                mA[base + j] = ha * scale; mB[base + j] = hb * scale;
             }
             __syncwarp();
             if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, E);
             row_load(yo - s.lo, L);
 #pragma unroll
             for (int jj = 0; jj < GC; ++jj) {
+                // straight-line for all lanes (the five chains interleave); stores and counts are predicated
                 const int i = s.lane + 32 * jj;
                 const int x = s.xs + i;
-                if (i >= s.outw || x >= a.W) continue;
+                const bool ok = i < s.outw && x < a.W;
                 const int r0 = pixw[jj] & 255, g0 = (pixw[jj] >> 8) & 255, b0 = (pixw[jj] >> 16) & 255;
                 double t = __dadd_rn(__dmul_rn(mA[i], sI[pixw[jj] >> 24]), mB[i]);
                 t = t < 0.1 ? 0.1 : (t > 1.0 ? 1.0 : t);
-                // (img - A) in float32, / t and + A in float64, stored in the library's float type
+                // (img - A) in float32, / t and + A in float64, stored in the library's float type.
+                // t is in [0.1, 1] and img - A is 0 or far above the subnormals: *_rn_normal are exact IEEE
                 double q0, q1, q2;
                 if (sizeof(T) == 8) {
-                    q0 = __ddiv_rn((double)sdiff[0][r0], t);
-                    q1 = __ddiv_rn((double)sdiff[1][g0], t);
-                    q2 = __ddiv_rn((double)sdiff[2][b0], t);
+                    q0 = div_rn_normal((double)sdiff[0][r0], t);
+                    q1 = div_rn_normal((double)sdiff[1][g0], t);
+                    q2 = div_rn_normal((double)sdiff[2][b0], t);
                 } else {
                     // float32 buffers: x * (1/t) differs from x / t by at most 1 ulp of float64, which
                     // survives the rounding to float32 with probability ~1e-8 per value
-                    const double it = __drcp_rn(t);
+                    const double it = rcp_rn_normal(t);
                     q0 = __dmul_rn((double)sdiff[0][r0], it);
                     q1 = __dmul_rn((double)sdiff[1][g0], it);
                     q2 = __dmul_rn((double)sdiff[2][b0], it);
@@ -324,11 +331,13 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
                 const T v0 = clip01<T>((T)__dadd_rn(q0, dl0));
                 const T v1 = clip01<T>((T)__dadd_rn(q1, dl1));
                 const T v2 = clip01<T>((T)__dadd_rn(q2, dl2));
-                T* o = out + (size_t)(ro + x) * 3;
-                o[0] = v0; o[1] = v1; o[2] = v2;
-                atomicAdd(&shist[0 * kSelBinsA + sel_bin_a<T>(v0)], 1u);
-                atomicAdd(&shist[1 * kSelBinsA + sel_bin_a<T>(v1)], 1u);
-                atomicAdd(&shist[2 * kSelBinsA + sel_bin_a<T>(v2)], 1u);
+                if (ok) {
+                    T* o = out + (size_t)(ro + x) * 3;
+                    o[0] = v0; o[1] = v1; o[2] = v2;
+                    atomicAdd(&shist[0 * kSelBinsA + sel_bin_a<T>(v0)], 1u);
+                    atomicAdd(&shist[1 * kSelBinsA + sel_bin_a<T>(v1)], 1u);
+                    atomicAdd(&shist[2 * kSelBinsA + sel_bin_a<T>(v2)], 1u);
+                }
             }
             __syncwarp();
 #pragma unroll
@@ -343,7 +352,46 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
     }
 }
 
+// ------------------------------------------------------------------ self-test of *_rn_normal
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+    z += 0x9E3779B97F4A7C15ull; z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; return z ^ (z >> 31);
+}
+// log-uniform magnitude in [2^lo, 2^hi) with a full random mantissa
+__device__ __forceinline__ double rand_mag(unsigned long long h, int lo, int hi) {
+    const int e = lo + (int)((h >> 52) % (unsigned)(hi - lo));
+    const unsigned long long bits = ((unsigned long long)(e + 1023) << 52) | (h & 0xFFFFFFFFFFFFFull);
+    return __longlong_as_double((long long)bits);
+}
+__global__ void selftest_div_kernel(unsigned long long count, unsigned long long seed, unsigned long long* bad) {
+    unsigned long long mine = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < count;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long h0 = mix64(seed + 3 * i), h1 = mix64(seed + 3 * i + 1), h2 = mix64(seed + 3 * i + 2);
+        const double y = rand_mag(h0, -30, 1);                       // [9.3e-10, 2)
+        double x = rand_mag(h1, -60, 1);                             // [8.7e-19, 2)
+        if (h2 & 1) x = -x;
+        if ((h2 & 0xfe) == 0) x = 0.0;
+        const double t = 0.1 + (double)(h2 >> 11) * (0.9 / 9007199254740992.0);
+        const double tt = t > 1.0 ? 1.0 : t;
+        if (__double_as_longlong(div_rn_normal(x, y)) != __double_as_longlong(__ddiv_rn(x, y))) ++mine;
+        if (__double_as_longlong(div_rn_normal(x, tt)) != __double_as_longlong(__ddiv_rn(x, tt))) ++mine;
+        if (__double_as_longlong(rcp_rn_normal(tt)) != __double_as_longlong(__drcp_rn(tt))) ++mine;
+    }
+    if (mine) atomicAdd(bad, mine);
+}
+
 }  // namespace
+
+int selftest_division(unsigned long long count, unsigned long long seed, unsigned long long* mismatches_host) {
+    unsigned long long* bad = nullptr;
+    if (cudaMalloc(&bad, 8) != cudaSuccess) return 1;
+    cudaMemset(bad, 0, 8);
+    selftest_div_kernel<<<148 * 8, 256>>>(count, seed, bad);
+    const cudaError_t rc = cudaMemcpy(mismatches_host, bad, 8, cudaMemcpyDeviceToHost);
+    cudaFree(bad);
+    return rc == cudaSuccess ? 0 : 1;
+}
 
 int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st) {
     if (a.n_dehaze == 0) return 0;
@@ -361,8 +409,13 @@ int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st) {
     const int bx = (strips + GWARPS - 1) / GWARPS;
     const int nt = 32 * ((strips + bx - 1) / bx);
     dim3 grid(bx, chunks, inst);
-    if (a.lib.clip_t0) gf_ab_kernel<true><<<grid, nt, 0, st>>>(a);
-    else gf_ab_kernel<false><<<grid, nt, 0, st>>>(a);
+    if (a.lib.clip_t0) {
+        if (a.eps_safe) gf_ab_kernel<true, true><<<grid, nt, 0, st>>>(a);
+        else gf_ab_kernel<true, false><<<grid, nt, 0, st>>>(a);
+    } else {
+        if (a.eps_safe) gf_ab_kernel<false, true><<<grid, nt, 0, st>>>(a);
+        else gf_ab_kernel<false, false><<<grid, nt, 0, st>>>(a);
+    }
     static const bool optin = [] {
         return cudaFuncSetAttribute(gf_recover_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RecoverShared)) == cudaSuccess &&
                cudaFuncSetAttribute(gf_recover_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RecoverShared)) == cudaSuccess;

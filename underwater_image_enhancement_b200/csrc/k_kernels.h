@@ -90,6 +90,7 @@ struct GuidedArgs {
     int n_dehaze;                // number of dehaze strategies
     int dehaze_idx[kStrategiesMax];   // their strategy indices
     int rows_per_block;
+    int eps_safe;                // every dehaze strategy has eps >= 1e-9: a = cov / (var + eps) needs no range check
     uint2* gd_plane;             // [B][H][W]   {R | G << 8 | B << 16 | gray << 24 of the (colour-corrected) frame,
                                  //              float32 bits of min_c img / (A + guard)}
     const uint8_t* frames;
@@ -100,6 +101,7 @@ struct GuidedArgs {
     unsigned* sel_hist_a;        // [B * n_dehaze][3][kSelBinsA]
 };
 int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st);
+int selftest_division(unsigned long long count, unsigned long long seed, unsigned long long* mismatches_host);
 
 struct SelTarget {
     long long rank;      // rank still to resolve inside the current bin

@@ -63,6 +63,7 @@ struct uwie_engine {
     int dehaze_idx[kStrategiesMax];
     int dehaze_slot[kStrategiesMax];
     int max_radius = 0, max_tiles = 0;
+    int eps_safe = 1;            // every dehaze eps >= 1e-9 (k_guided.cu: division without a range check)
     bool need_hist_pass = false;
     int final_blocks = 0, pix_per_block = 0;
     std::vector<std::pair<int, int>> quad_dims;   // per level: max quadrant rows, cols
@@ -206,7 +207,7 @@ int init_engine_shape(uwie_engine* e, const uwie_library* lib, const uwie_strate
     int rc = build_recipes(lib, st, n, H, W, &e->lib, &e->recipes);
     if (rc) return rc;
     e->S = n; e->B = B; e->H = H; e->W = W;
-    e->n_dehaze = 0; e->max_radius = 0; e->max_tiles = 0; e->need_hist_pass = false;
+    e->n_dehaze = 0; e->max_radius = 0; e->max_tiles = 0; e->need_hist_pass = false; e->eps_safe = 1;
     for (int i = 0; i < kStrategiesMax; ++i) { e->dehaze_idx[i] = 0; e->dehaze_slot[i] = -1; }
     for (int i = 0; i < n; ++i) {
         const Recipe& r = e->recipes[i];
@@ -214,6 +215,7 @@ int init_engine_shape(uwie_engine* e, const uwie_library* lib, const uwie_strate
             e->dehaze_slot[i] = e->n_dehaze;
             e->dehaze_idx[e->n_dehaze++] = i;
             if (r.radius > e->max_radius) e->max_radius = r.radius;
+            if (!(r.eps >= 1e-9 && r.eps <= 1e9)) e->eps_safe = 0;
         }
         if (r.clahe) {
             if (r.tiles_x * r.tiles_y > e->max_tiles) e->max_tiles = r.tiles_x * r.tiles_y;
@@ -242,6 +244,12 @@ int init_engine_shape(uwie_engine* e, const uwie_library* lib, const uwie_strate
 extern "C" {
 
 int uwie_version(void) { return UWIE_VERSION; }
+
+int uwie_selftest_division(unsigned long long count, unsigned long long seed, unsigned long long* mismatches_host) {
+    if (!mismatches_host) return fail(UWIE_ERR_ARG, "null mismatch counter");
+    if (uwie::selftest_division(count, seed, mismatches_host)) return fail(UWIE_ERR_CUDA, "division self-test did not run");
+    return UWIE_OK;
+}
 const char* uwie_last_error(void) { return g_err.c_str(); }
 
 int uwie_preset(int library_id, uwie_library* lib, uwie_strategy* st) {
@@ -464,6 +472,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
             ga.rows_per_block = (H + chunks - 1) / chunks;
         }
         ga.gd_plane = e->at<uint2>(L.gf_gray);
+        ga.eps_safe = e->eps_safe;
         ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;
         ga.ab = e->at<double2>(L.ab); ga.recovered = e->at<void>(L.recovered);
         ga.sel_hist_a = e->at<unsigned>(L.sel_hist_a);
