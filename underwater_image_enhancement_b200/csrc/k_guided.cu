@@ -302,6 +302,15 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
                 mA[base + j] = ha * scale; mB[base + j] = hb * scale;
             }
             __syncwarp();
+            // transmission of the five pixels first: it consumes this row's pixel words, so the row loads
+            // that follow do not sit in front of them in the load queue
+            double tt[GC];
+#pragma unroll
+            for (int jj = 0; jj < GC; ++jj) {
+                const int i = s.lane + 32 * jj;
+                const double t = __dadd_rn(__dmul_rn(mA[i], sI[pixw[jj] >> 24]), mB[i]);
+                tt[jj] = t < 0.1 ? 0.1 : (t > 1.0 ? 1.0 : t);
+            }
             if (yo + 1 < s.ye) row_load(yo + 1 + s.hi, E);
             row_load(yo - s.lo, L);
 #pragma unroll
@@ -311,8 +320,7 @@ __global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
                 const int x = s.xs + i;
                 const bool ok = i < s.outw && x < a.W;
                 const int r0 = pixw[jj] & 255, g0 = (pixw[jj] >> 8) & 255, b0 = (pixw[jj] >> 16) & 255;
-                double t = __dadd_rn(__dmul_rn(mA[i], sI[pixw[jj] >> 24]), mB[i]);
-                t = t < 0.1 ? 0.1 : (t > 1.0 ? 1.0 : t);
+                const double t = tt[jj];
                 // (img - A) in float32, / t and + A in float64, stored in the library's float type.
                 // t is in [0.1, 1] and img - A is 0 or far above the subnormals: *_rn_normal are exact IEEE
                 double q0, q1, q2;
