@@ -7,7 +7,7 @@ TAG=${1:?tag}
 mkdir -p gpurun_out
 timeout 600 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
 timeout 600 python bench.py --impl reference > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err
-ONE="python bench.py --batch 8 --lanes 1 --steps 1 --warmup 1 --e2e-frames 8 --no-cpu-baseline"
+ONE="python bench.py --batch 16 --chunk 16 --lanes 1 --steps 1 --warmup 1 --e2e-frames 16 --e2e-chunk 16 --no-cpu-baseline"
 UWIE_HOST_ONE_LANE=1 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $ONE > gpurun_out/${TAG}_launches.log 2>&1
 UWIE_HOST_ONE_LANE=1 timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled \

@@ -33,7 +33,7 @@ _LIB.define("vgg_features(Tensor frames) -> Tensor")
 _LIB.define("vgg_preprocess(Tensor frames, int size) -> Tensor")
 
 _ENGINES: dict = {}
-_CHUNK = 8           # frames per engine call: the working set of a chunk stays near the L2
+_CHUNK = 16          # frames per engine call: fewer, fuller launches (bench.py --chunk)
 
 
 def _engine(library, frames):
