@@ -18,59 +18,79 @@ constexpr int NT = 128;
 __device__ __forceinline__ float clipf(float x, float lo, float hi) { return x < lo ? lo : (x > hi ? hi : x); }
 __device__ __forceinline__ double clipd(double x, double lo, double hi) { return x < lo ? lo : (x > hi ? hi : x); }
 
+// fixed-order tree sums of K per-thread values over the block (deterministic run to run)
+template <int K>
+__device__ __forceinline__ void block_sums(double (&v)[K], double (*red)[NT]) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) red[k][threadIdx.x] = v[k];
+    __syncthreads();
+    for (int o = NT / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) red[k][threadIdx.x] += red[k][threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) v[k] = red[k][0];
+    __syncthreads();
+}
+
 __global__ void __launch_bounds__(NT) score_kernel(ScoreArgs a) {
     const int s = blockIdx.x, b = blockIdx.y;
     const size_t bs = (size_t)b * a.S + s;
     const QaAccum& acc = a.qa[bs];
     const double n = (double)a.n;
-    __shared__ double red[NT];
-    __shared__ double cf[4];
-    // colourfulness moments: fixed-order reduction of the per-block partials
-    for (int k = 0; k < 4; ++k) {
-        double t = 0.0;
-        for (int i = threadIdx.x; i < a.final_blocks; i += NT) t += a.cf_part[(bs * a.final_blocks + i) * 4 + k];
-        red[threadIdx.x] = t;
-        __syncthreads();
-        for (int o = NT / 2; o > 0; o >>= 1) {
-            if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
-            __syncthreads();
-        }
-        if (threadIdx.x == 0) cf[k] = red[0];
-        __syncthreads();
+    __shared__ double red[10][NT];
+    // every thread takes bins tid and tid + 128 of the histograms and a slice of the per-block colourfulness
+    // partials; ten sums leave in one tree reduction, the variance of the gray values in a second one
+    double q[10];
+#pragma unroll
+    for (int k = 0; k < 10; ++k) q[k] = 0.0;
+    for (int i = threadIdx.x; i < a.final_blocks; i += NT) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) q[k] += a.cf_part[(bs * a.final_blocks + i) * 4 + k];
     }
+    unsigned hg[2], hs[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int v = threadIdx.x + h * NT;
+        hg[h] = acc.gray_hist[v]; hs[h] = acc.sat_hist[v];
+        const float fv = __fdiv_rn((float)v, 255.0f);
+        q[4] += (double)hg[h] * (double)fv;                                      // mean of gray/255
+        if (hg[h]) { const double pk = (double)hg[h] / n; q[5] += -pk * log(pk); }   // entropy terms
+        q[6] += (double)hs[h] * (double)fv;                                      // mean of S/255
+        if (fv > 0.9f) { q[7] += (double)hs[h]; q[9] += (double)hg[h]; }         // over-saturated, bright
+        if (fv < 0.1f) q[8] += (double)hg[h];                                    // dark
+    }
+    block_sums<10>(q, red);
+    const double cf[4] = {q[0], q[1], q[2], q[3]};
+    const double gmean = q[4] / n;
+    double var[1] = {0.0};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const double d = (double)__fdiv_rn((float)(threadIdx.x + h * NT), 255.0f) - gmean;
+        var[0] += (double)hg[h] * d * d;
+    }
+    block_sums<1>(var, red);
     if (threadIdx.x != 0) return;
 
     double sub[8];
     int is_f32[8] = {1, 0, 0, 1, 1, 0, a.lib.f64 ? 0 : 1, 0};
     // contrast: std of gray/255 (float32 data)                                   QA:25-31
     {
-        double m = 0.0;
-        for (int v = 0; v < 256; ++v) m += (double)acc.gray_hist[v] * (double)__fdiv_rn((float)v, 255.0f);
-        m /= n;
-        double var = 0.0;
-        for (int v = 0; v < 256; ++v) {
-            const double d = (double)__fdiv_rn((float)v, 255.0f) - m;
-            var += (double)acc.gray_hist[v] * d * d;
-        }
-        const float sd = (float)sqrt(var / n);
+        const float sd = (float)sqrt(var[0] / n);
         sub[0] = (double)clipf(__fmul_rn(__fdiv_rn(sd, 0.5f), 100.0f), 0.f, 100.f);
     }
     sub[1] = 50.0;                                                               // QA:49, 250-251
     // entropy of the gray value counts, scipy.stats.entropy(counts, base=2)       QA:68-73
     {
-        double S = 0.0;
-        for (int v = 0; v < 256; ++v) {
-            const unsigned c = acc.gray_hist[v];
-            if (c) { const double pk = (double)c / n; S += -pk * log(pk); }
-        }
-        S /= log(2.0);
+        const double S = q[5] / log(2.0);
         sub[2] = clipd((S - 4.0) / 4.0 * 100.0, 0.0, 100.0);
     }
     // saturation: mean of S/255 (float32)                                         QA:88-95
     {
-        double m = 0.0;
-        for (int v = 0; v < 256; ++v) m += (double)acc.sat_hist[v] * (double)__fdiv_rn((float)v, 255.0f);
-        const float ms = (float)(m / n);
+        const float ms = (float)(q[6] / n);
         sub[3] = (double)clipf(__fmul_rn(ms, 100.0f), 0.f, 100.f);
     }
     // brightness: 100 - clip(|mean(L) - 128| / 128 * 100) (float32)               QA:111-121
@@ -100,13 +120,8 @@ __global__ void __launch_bounds__(NT) score_kernel(ScoreArgs a) {
     }
     // naturalness (float64 ratios of float32 comparisons)                         QA:198-210
     {
-        unsigned long long over = 0, dark = 0, bright = 0;
-        for (int v = 0; v < 256; ++v) {
-            const float fv = __fdiv_rn((float)v, 255.0f);
-            if (fv > 0.9f) { over += acc.sat_hist[v]; bright += acc.gray_hist[v]; }
-            if (fv < 0.1f) dark += acc.gray_hist[v];
-        }
-        const double ratio = (double)over / n + (double)dark / n + (double)bright / n;
+        // counts below 2^53: the float64 sums above are exact
+        const double ratio = q[7] / n + q[8] / n + q[9] / n;
         sub[7] = 100.0 - clipd(ratio * 200.0, 0.0, 100.0);
     }
     // total = sum(scores[k] * weights.get(k, 0)) with NumPy's scalar promotions    QA:284
