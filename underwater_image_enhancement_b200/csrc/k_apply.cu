@@ -196,9 +196,11 @@ struct ApplyShared {
 
 template <class T> struct Vec4 { T v[4][3]; };
 
-template <class T, bool FINAL>
+// CLAHE / DEHAZE: the strategy's path is fixed at compile time (one launch per variant present in the
+// library), so a pixel runs straight-line code and a kernel carries only its own path.
+template <class T, bool FINAL, bool CLAHE, bool DEHAZE>
 __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
-    const int s = blockIdx.y, b = blockIdx.z;
+    const int s = a.var_s[(CLAHE ? 2 : 0) + (DEHAZE ? 1 : 0)][blockIdx.y], b = blockIdx.z;
     const Recipe& rc = a.recipes[s];
     if (!FINAL && !(rc.clahe && rc.n_post > 0)) return;
     const StratTables& st = a.tables[(size_t)b * a.S + s];
@@ -218,7 +220,7 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
             (&s_postf[0][0])[i] = (T)(&st.postf[0][0])[i];
         }
     }
-    const bool clahe = rc.clahe != 0, dehaze = rc.dehaze != 0;
+    constexpr bool clahe = CLAHE, dehaze = DEHAZE;
     const int n_pre = rc.n_pre;
     T lo[kMaxStretch][3], den[kMaxStretch][3];
 #pragma unroll
@@ -402,16 +404,26 @@ int launch_clahe_luts(const ApplyArgs& a, int max_tiles, cudaStream_t st) {
     return 1;
 }
 
-int launch_apply(const ApplyArgs& a, bool final_pass, cudaStream_t st) {
-    dim3 grid(a.final_blocks, a.S, a.B);
-    if (a.lib.f64) {
-        if (final_pass) apply_kernel<double, true><<<grid, NT, 0, st>>>(a);
-        else apply_kernel<double, false><<<grid, NT, 0, st>>>(a);
-    } else {
-        if (final_pass) apply_kernel<float, true><<<grid, NT, 0, st>>>(a);
-        else apply_kernel<float, false><<<grid, NT, 0, st>>>(a);
+template <class T, bool FINAL>
+int launch_apply_t(const ApplyArgs& a, cudaStream_t st) {
+    int launches = 0;
+    for (int v = FINAL ? 0 : 2; v < 4; ++v) {              // the histogram pass exists for CLAHE strategies only
+        if (a.var_n[v] == 0) continue;
+        dim3 grid(a.final_blocks, a.var_n[v], a.B);
+        switch (v) {
+            case 0: apply_kernel<T, FINAL, false, false><<<grid, NT, 0, st>>>(a); break;
+            case 1: apply_kernel<T, FINAL, false, true><<<grid, NT, 0, st>>>(a); break;
+            case 2: apply_kernel<T, FINAL, true, false><<<grid, NT, 0, st>>>(a); break;
+            default: apply_kernel<T, FINAL, true, true><<<grid, NT, 0, st>>>(a); break;
+        }
+        ++launches;
     }
-    return 1;
+    return launches;
+}
+
+int launch_apply(const ApplyArgs& a, bool final_pass, cudaStream_t st) {
+    if (a.lib.f64) return final_pass ? launch_apply_t<double, true>(a, st) : launch_apply_t<double, false>(a, st);
+    return final_pass ? launch_apply_t<float, true>(a, st) : launch_apply_t<float, false>(a, st);
 }
 
 }  // namespace uwie

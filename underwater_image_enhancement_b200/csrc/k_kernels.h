@@ -137,6 +137,8 @@ struct ApplyArgs {
     const Recipe* recipes;
     int n_dehaze;
     int dehaze_slot[kStrategiesMax];   // strategy -> slot in the recovered buffer, -1 if none
+    int var_n[4];                      // strategies per kernel variant (clahe * 2 + dehaze) and their indices:
+    int var_s[4][kStrategiesMax];      // every variant is its own instantiation of apply_kernel
     const uint8_t* frames;
     const StratTables* tables;
     const void* recovered;

@@ -501,6 +501,10 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     aa.B = batch; aa.S = S; aa.H = H; aa.W = W; aa.lib = e->lib; aa.recipes = sa.recipes;
     aa.n_dehaze = e->n_dehaze;
     for (int i = 0; i < kStrategiesMax; ++i) aa.dehaze_slot[i] = e->dehaze_slot[i];
+    for (int i = 0; i < S; ++i) {
+        const int v = (e->recipes[i].clahe ? 2 : 0) + (e->recipes[i].dehaze ? 1 : 0);
+        aa.var_s[v][aa.var_n[v]++] = i;
+    }
     aa.frames = frames; aa.tables = sa.tables; aa.recovered = e->at<void>(L.recovered);
     aa.ctab = e->at<ColorTables>(L.ctab);
     aa.tile_lut = e->at<uint8_t>(L.tile_lut);
