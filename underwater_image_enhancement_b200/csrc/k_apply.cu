@@ -162,23 +162,40 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
     a.tile_lut[(((size_t)b * a.S + s) * kMaxTiles + blockIdx.x) * 256 + t] = clahe_lut_entry(base + incl, clahe_lut_scale(area));
 }
 
-__device__ __forceinline__ int clahe_interp(const uint8_t* luts, int tiles_x, int tiles_y, float inv_tw,
-                                            float inv_th, int y, int x, int v) {
-    const float txf = __fsub_rn(__fmul_rn((float)x, inv_tw), 0.5f);
+// cv2 CLAHE interpolation (modules/imgproc/src/clahe.cpp, CLAHE_Interpolation_Body): the row part (tile rows
+// ty1 / ty2 and their weights) is shared by the pixels of a row, the column part is per pixel.
+struct ClaheRow {
+    int off1, off2;          // byte offsets of the LUT rows ty1, ty2
+    float ya, ya1;
+};
+__device__ __forceinline__ ClaheRow clahe_row(int tiles_x, int tiles_y, float inv_th, int y) {
     const float tyf = __fsub_rn(__fmul_rn((float)y, inv_th), 0.5f);
-    int tx1 = (int)floorf(txf), ty1 = (int)floorf(tyf);
-    const float xa = __fsub_rn(txf, (float)tx1), ya = __fsub_rn(tyf, (float)ty1);
-    const float xa1 = __fsub_rn(1.0f, xa), ya1 = __fsub_rn(1.0f, ya);
-    int tx2 = tx1 + 1, ty2 = ty1 + 1;
-    tx1 = max(tx1, 0); ty1 = max(ty1, 0);
-    tx2 = min(tx2, tiles_x - 1); ty2 = min(ty2, tiles_y - 1);
-    const float l11 = (float)luts[((size_t)ty1 * tiles_x + tx1) * 256 + v];
-    const float l12 = (float)luts[((size_t)ty1 * tiles_x + tx2) * 256 + v];
-    const float l21 = (float)luts[((size_t)ty2 * tiles_x + tx1) * 256 + v];
-    const float l22 = (float)luts[((size_t)ty2 * tiles_x + tx2) * 256 + v];
+    int ty1 = (int)floorf(tyf);
+    ClaheRow r;
+    r.ya = __fsub_rn(tyf, (float)ty1);
+    r.ya1 = __fsub_rn(1.0f, r.ya);
+    int ty2 = ty1 + 1;
+    ty1 = max(ty1, 0);
+    ty2 = min(ty2, tiles_y - 1);
+    r.off1 = ty1 * tiles_x * 256; r.off2 = ty2 * tiles_x * 256;
+    return r;
+}
+__device__ __forceinline__ int clahe_interp(const uint8_t* luts, int tiles_x, float inv_tw, const ClaheRow& row, int x, int v) {
+    const float txf = __fsub_rn(__fmul_rn((float)x, inv_tw), 0.5f);
+    int tx1 = (int)floorf(txf);
+    const float xa = __fsub_rn(txf, (float)tx1);
+    const float xa1 = __fsub_rn(1.0f, xa);
+    int tx2 = tx1 + 1;
+    tx1 = max(tx1, 0);
+    tx2 = min(tx2, tiles_x - 1);
+    const int c1 = tx1 * 256 + v, c2 = tx2 * 256 + v;
+    const float l11 = (float)luts[row.off1 + c1];
+    const float l12 = (float)luts[row.off1 + c2];
+    const float l21 = (float)luts[row.off2 + c1];
+    const float l22 = (float)luts[row.off2 + c2];
     const float top = __fadd_rn(__fmul_rn(l11, xa1), __fmul_rn(l12, xa));
     const float bot = __fadd_rn(__fmul_rn(l21, xa1), __fmul_rn(l22, xa));
-    const float res = __fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya));
+    const float res = __fadd_rn(__fmul_rn(top, row.ya1), __fmul_rn(bot, row.ya));
     return clampi(__float2int_rn(res), 0, 255);
 }
 
@@ -260,7 +277,7 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
     };
     // one pixel: bytes (no-dehaze) or floats (dehaze) in -> float value f and byte q per channel out.
     // Returns false when the pixel only feeds the HIST pass.
-    auto shade = [&](int r8, int g8, int b8, T fr, T fg, T fb, int y, int x, T* f, int* q) -> bool {
+    auto shade = [&](int r8, int g8, int b8, T fr, T fg, T fb, const ClaheRow& row, int x, T* f, int* q) -> bool {
         if (clahe) {
             int r, g, bl, L, A, Bc;
             if (!dehaze) { r = sm.preq[0][r8]; g = sm.preq[1][g8]; bl = sm.preq[2][b8]; }
@@ -270,7 +287,7 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
                 r = quantise<T>(v0); g = quantise<T>(v1); bl = quantise<T>(v2);
             }
             rgb_to_lab(sm.ct.gamma_in, sm.ct.cbrt_tab, r, g, bl, L, A, Bc);
-            L = clahe_interp(luts, tiles_x, tiles_y, inv_tw, inv_th, y, x, L);
+            L = clahe_interp(luts, tiles_x, inv_tw, row, x, L);
             int k0, k1, k2;
             lab_to_rgb(sm.ct.lab_yf, sm.ct.gamma_out, L, A, Bc, k0, k1, k2);
             if (!FINAL) {
@@ -323,30 +340,34 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
             for (int i = 0; i < 12; ++i) d[i] = rec[(size_t)p * 3 + i];
         }
         int y = 0, x = 0;
-        if (clahe) { y = (int)(p / (unsigned)a.W); x = (int)(p - (unsigned)y * (unsigned)a.W); }
+        ClaheRow row = {0, 0, 0.f, 0.f};
+        if (clahe) {
+            y = (int)(p / (unsigned)a.W); x = (int)(p - (unsigned)y * (unsigned)a.W);
+            row = clahe_row(tiles_x, tiles_y, inv_th, y);
+        }
         uint32_t o0 = 0, o1 = 0, o2 = 0, gw = 0;
         T f[3];
         int q[3];
         // pixel 0: bytes 0..2
-        if (shade(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255, d[0], d[1], d[2], y, x, f, q)) {
+        if (shade(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255, d[0], d[1], d[2], row, x, f, q)) {
             o0 = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16);
             gw = (uint32_t)account(f, q);
         }
-        if (++x == a.W) { x = 0; ++y; }
+        if (++x == a.W) { x = 0; ++y; if (clahe) row = clahe_row(tiles_x, tiles_y, inv_th, y); }
         // pixel 1: bytes 3..5
-        if (shade(w0 >> 24, w1 & 255, (w1 >> 8) & 255, d[3], d[4], d[5], y, x, f, q)) {
+        if (shade(w0 >> 24, w1 & 255, (w1 >> 8) & 255, d[3], d[4], d[5], row, x, f, q)) {
             o0 |= (uint32_t)q[0] << 24; o1 = (uint32_t)q[1] | ((uint32_t)q[2] << 8);
             gw |= (uint32_t)account(f, q) << 8;
         }
-        if (++x == a.W) { x = 0; ++y; }
+        if (++x == a.W) { x = 0; ++y; if (clahe) row = clahe_row(tiles_x, tiles_y, inv_th, y); }
         // pixel 2: bytes 6..8
-        if (shade((w1 >> 16) & 255, w1 >> 24, w2 & 255, d[6], d[7], d[8], y, x, f, q)) {
+        if (shade((w1 >> 16) & 255, w1 >> 24, w2 & 255, d[6], d[7], d[8], row, x, f, q)) {
             o1 |= ((uint32_t)q[0] << 16) | ((uint32_t)q[1] << 24); o2 = (uint32_t)q[2];
             gw |= (uint32_t)account(f, q) << 16;
         }
-        if (++x == a.W) { x = 0; ++y; }
+        if (++x == a.W) { x = 0; ++y; if (clahe) row = clahe_row(tiles_x, tiles_y, inv_th, y); }
         // pixel 3: bytes 9..11
-        if (shade((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24, d[9], d[10], d[11], y, x, f, q)) {
+        if (shade((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24, d[9], d[10], d[11], row, x, f, q)) {
             o2 |= ((uint32_t)q[0] << 8) | ((uint32_t)q[1] << 16) | ((uint32_t)q[2] << 24);
             gw |= (uint32_t)account(f, q) << 24;
         }
@@ -363,7 +384,8 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
         int q[3];
         if (dehaze) { d0 = rec[(size_t)p * 3]; d1 = rec[(size_t)p * 3 + 1]; d2 = rec[(size_t)p * 3 + 2]; }
         const int y = (int)(p / (unsigned)a.W), x = (int)(p - (unsigned)y * (unsigned)a.W);
-        if (shade(fp[0], fp[1], fp[2], d0, d1, d2, y, x, f, q)) {
+        const ClaheRow row = clahe ? clahe_row(tiles_x, tiles_y, inv_th, y) : ClaheRow{0, 0, 0.f, 0.f};
+        if (shade(fp[0], fp[1], fp[2], d0, d1, d2, row, x, f, q)) {
             out[(size_t)p * 3] = (uint8_t)q[0]; out[(size_t)p * 3 + 1] = (uint8_t)q[1]; out[(size_t)p * 3 + 2] = (uint8_t)q[2];
             gray[p] = (uint8_t)account(f, q);
         }
