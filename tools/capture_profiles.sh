@@ -12,5 +12,5 @@ UWIE_HOST_ONE_LANE=1 timeout 600 ncu --metrics gpu__time_duration.sum --clock-co
     --log-file gpurun_out/${TAG}_launches.csv $ONE > gpurun_out/${TAG}_launches.log 2>&1
 UWIE_HOST_ONE_LANE=1 timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled \
     -k regex:"gf_ab_kernel|gf_recover_kernel|sel_hist_kernel|apply_kernel|clahe_lut_kernel|canny_tile_kernel<.int.1>|canny_rim_kernel<.bool.1>|canny_list_kernel|score_kernel|gf_prep" \
-    -c 14 -o gpurun_out/${TAG}_full $ONE > gpurun_out/${TAG}_full.log 2>&1
+    -c 30 -o gpurun_out/${TAG}_full $ONE > gpurun_out/${TAG}_full.log 2>&1
 tail -c 600 gpurun_out/${TAG}_bench.json

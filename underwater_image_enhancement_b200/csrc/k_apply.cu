@@ -430,7 +430,7 @@ template <class T, bool FINAL>
 int launch_apply_t(const ApplyArgs& a, cudaStream_t st) {
     int launches = 0;
     for (int v = FINAL ? 0 : 2; v < 4; ++v) {              // the histogram pass exists for CLAHE strategies only
-        if (a.var_n[v] == 0) continue;
+        if (a.var_n[v] == 0 || (!FINAL && a.var_hist[v] == 0)) continue;
         dim3 grid(a.final_blocks, a.var_n[v], a.B);
         switch (v) {
             case 0: apply_kernel<T, FINAL, false, false><<<grid, NT, 0, st>>>(a); break;

@@ -139,6 +139,7 @@ struct ApplyArgs {
     int dehaze_slot[kStrategiesMax];   // strategy -> slot in the recovered buffer, -1 if none
     int var_n[4];                      // strategies per kernel variant (clahe * 2 + dehaze) and their indices:
     int var_s[4][kStrategiesMax];      // every variant is its own instantiation of apply_kernel
+    int var_hist[4];                   // strategies of the variant that need the histogram pass (CLAHE + post-stretches)
     const uint8_t* frames;
     const StratTables* tables;
     const void* recovered;

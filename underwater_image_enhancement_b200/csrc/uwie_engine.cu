@@ -504,6 +504,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     for (int i = 0; i < S; ++i) {
         const int v = (e->recipes[i].clahe ? 2 : 0) + (e->recipes[i].dehaze ? 1 : 0);
         aa.var_s[v][aa.var_n[v]++] = i;
+        if (e->recipes[i].clahe && e->recipes[i].n_post > 0) ++aa.var_hist[v];
     }
     aa.frames = frames; aa.tables = sa.tables; aa.recovered = e->at<void>(L.recovered);
     aa.ctab = e->at<ColorTables>(L.ctab);
