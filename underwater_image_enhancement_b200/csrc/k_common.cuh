@@ -14,6 +14,7 @@ constexpr int kSelBinsA = 1056;      // first-level bins of the percentile selec
 constexpr int kSelBinsB = 2048;      // second level: 11 bits
 constexpr int kSelBinsC = 1024;      // third level: 10 bits
 constexpr int kSelTargets = 24;      // 3 channels x 2 stretches x (lo, hi) x (k, k+1)
+constexpr int kSelListCap = 32768;   // members of a target's level-A bin kept as a list (bit patterns); a longer bin takes the streaming levels B / C
 constexpr int kSelTable = 256;       // distinct values ranked inside a final bin of width 2^-31 (hash table slots)
 constexpr int kQuadLevelsMax = 24;   // log2 of the largest supported side, with slack
 

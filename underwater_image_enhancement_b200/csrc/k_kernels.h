@@ -107,8 +107,9 @@ struct SelTarget {
     long long rank;      // rank still to resolve inside the current bin
     unsigned prefix;     // digits of the key resolved so far (11, 22, then all 32 bits)
     int active;
-    int rep;             // target of the same channel whose histogram / table this one shares
+    int rep;             // target of the same channel whose histogram / table / list this one shares
     int pad;
+    double val;          // active == 3: the order statistic itself (resolved from the candidate list)
 };
 struct SelectArgs {
     int B, S;
@@ -124,6 +125,9 @@ struct SelectArgs {
     SelTarget* targets;          // [inst][kSelTargets]
     unsigned long long* tab_keys;   // [inst][kSelTargets][kSelTable], 0 = empty, else bit pattern + 1
     unsigned* tab_counts;           // [inst][kSelTargets][kSelTable]
+    void* cand;                     // [inst][kSelTargets][kSelListCap] bit patterns (32 / 64 bits) of the members of a target's level-A bin
+    unsigned* cand_n;               // [inst][kSelTargets] members seen (may exceed kSelListCap: list unusable)
+    unsigned* stats;                // [2] targets resolved from lists / targets sent down the streaming levels (diagnostics)
     StratTables* tables;         // [B][S]
     int* status;
 };

@@ -82,7 +82,10 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
         T.rank = rank - acc;
         if (LEVEL == 0) {
             // bin 0 of level A holds the exact zeros (clipping makes them very common): resolved at once
-            if (bin == 0) T.active = 2; else T.prefix = (unsigned)(bin - 1);
+            // and the last bin (key >> 21 == 1024) holds nothing but exact ones: the recovered frame is clipped to [0, 1]
+            if (bin == 0) T.active = 2;
+            else if (bin == 1025) T.active = 4;
+            else T.prefix = (unsigned)(bin - 1);
         } else {
             T.prefix = (T.prefix << bits) | (unsigned)bin;
         }
@@ -102,6 +105,10 @@ __global__ void __launch_bounds__(kSelTargets * 32) sel_scan_kernel(SelectArgs a
         T.rep = rep;
     }
 }
+
+template <class T> struct SelBits;
+template <> struct SelBits<float> { using type = unsigned; };
+template <> struct SelBits<double> { using type = unsigned long long; };
 
 // Shared prologue of the streaming passes: the targets of this instance and, per channel, which
 // level-A bins hold a target at all.
@@ -205,9 +212,95 @@ __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
                 const int tg = ps.list[c][t];
                 const bool hit = hc && ps.pre[tg] == hi;
                 const unsigned hits = __ballot_sync(0xffffffffu, hit);
-                if (hit) agg_add(gh + (size_t)tg * BINS, sub, hits);
+                if (hit) {
+                    agg_add(gh + (size_t)tg * BINS, sub, hits);
+                    if (LEVEL == 1) {
+                        // the member itself goes to the target's candidate list (one atomic per warp)
+                        const int lane = threadIdx.x & 31, lead = __ffs(hits) - 1;
+                        unsigned base = 0;
+                        if (lane == lead) base = atomicAdd(&a.cand_n[(size_t)inst * kSelTargets + tg], (unsigned)__popc(hits));
+                        base = __shfl_sync(hits, base, lead) + (unsigned)__popc(hits & ((1u << lane) - 1u));
+                        if (base < (unsigned)kSelListCap)
+                            reinterpret_cast<typename SelBits<T>::type*>(a.cand)[((size_t)inst * kSelTargets + tg) * kSelListCap + base] =
+                                (typename SelBits<T>::type)sel_bits<T>(x[j]);
+                    }
+                }
             }
         }
+    }
+}
+
+// ---- candidate lists: a target whose level-A bin fitted its list is resolved here, with no further
+// streaming read: radix selection (8-bit digits, most significant first) over the bit patterns, which
+// order like the values because the recovered frame is >= 0.  One block per target.
+template <class T>
+__global__ void __launch_bounds__(NT) sel_small_kernel(SelectArgs a) {
+    using U = typename SelBits<T>::type;
+    constexpr int BITS = sizeof(U) * 8;
+    const int tg = blockIdx.x, inst = blockIdx.y;
+    SelTarget& Tt = a.targets[(size_t)inst * kSelTargets + tg];
+    if (Tt.active != 1) return;                                   // block-uniform
+    const int rep = Tt.rep;
+    const unsigned m = a.cand_n[(size_t)inst * kSelTargets + rep];
+    if (m > (unsigned)kSelListCap) {                              // list unusable: levels B / C resolve this one
+        if (threadIdx.x == 0) atomicAdd(&a.stats[1], 1u);
+        return;
+    }
+    const U* list = reinterpret_cast<const U*>(a.cand) + ((size_t)inst * kSelTargets + rep) * kSelListCap;
+    __shared__ unsigned hist[256];
+    __shared__ long long s_rank;
+    __shared__ int s_digit;
+    U prefix = 0;
+    if (threadIdx.x == 0) s_rank = Tt.rank;
+    const unsigned rounds = (m + NT - 1) / NT;
+    for (int shift = BITS - 8; shift >= 0; shift -= 8) {
+        hist[threadIdx.x] = 0;
+        __syncthreads();
+        for (unsigned rd = 0; rd < rounds; ++rd) {
+            const unsigned i = rd * NT + threadIdx.x;
+            bool in = i < m;
+            U v = 0;
+            if (in) { v = list[i]; in = shift == BITS - 8 || (v >> (shift + 8)) == prefix; }
+            const unsigned who = __ballot_sync(0xffffffffu, in);
+            if (in) agg_add(hist, (unsigned)(v >> shift) & 255u, who);
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            const int lane = threadIdx.x;
+            const long long rank = s_rank;
+            long long mine = 0;
+            for (int i = 0; i < 8; ++i) mine += hist[lane * 8 + i];
+            long long incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const long long v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const long long excl = incl - mine;
+            const bool here = excl <= rank && rank < incl;
+            if (__ballot_sync(0xffffffffu, here) == 0 && lane == 0) {     // cannot happen; keep the run alive and flag it
+                atomicOr(a.status, UWIE_STATUS_SELECT_INTERNAL);
+                s_digit = 0;
+            }
+            if (here) {
+                long long acc = excl;
+                int bin = lane * 8;
+                for (int i = 0; i < 8; ++i, ++bin) {
+                    const long long nx = acc + hist[bin];
+                    if (nx > rank) break;
+                    acc = nx;
+                }
+                s_rank = rank - acc;
+                s_digit = bin;
+            }
+        }
+        __syncthreads();
+        prefix = (prefix << 8) | (U)s_digit;
+    }
+    if (threadIdx.x == 0) {
+        Tt.val = (double)sel_from_bits<T>((unsigned long long)prefix);
+        Tt.active = 3;
+        atomicAdd(&a.stats[0], 1u);
     }
 }
 
@@ -284,6 +377,8 @@ __global__ void __launch_bounds__(NT) sel_finish_kernel(SelectArgs a) {
         const SelTarget t = a.targets[(size_t)inst * kSelTargets + tg];
         if (!t.active) continue;                       // uniform per block
         if (t.active == 2) { if (threadIdx.x == 0) s_val[tg] = 0.0; continue; }
+        if (t.active == 4) { if (threadIdx.x == 0) s_val[tg] = 1.0; continue; }
+        if (t.active == 3) { if (threadIdx.x == 0) s_val[tg] = t.val; continue; }
         if (sizeof(T) == 4 && t.prefix >= kExactKeyMin) {
             // key = x * 2^31 exactly, with at most 24 significant bits
             if (threadIdx.x == 0) s_val[tg] = (double)__fmul_rn(__uint2float_rn(t.prefix), 4.656612873077393e-10f);
@@ -358,6 +453,8 @@ int launch_select_t(const SelectArgs& a, int inst, cudaStream_t st) {
     if (vec) sel_hist_kernel<T, 1, true><<<dim3(nblk, inst), NT, 0, st>>>(a);
     else sel_hist_kernel<T, 1, false><<<dim3(nblk, inst), NT, 0, st>>>(a);
     ++launches;
+    sel_small_kernel<T><<<dim3(kSelTargets, inst), NT, 0, st>>>(a); ++launches;
+    // from here on only for targets whose list overflowed; otherwise every block exits in its prologue
     sel_scan_kernel<1><<<inst, kSelTargets * 32, 0, st>>>(a); ++launches;
     if (vec) sel_hist_kernel<T, 2, true><<<dim3(nblk, inst), NT, 0, st>>>(a);
     else sel_hist_kernel<T, 2, false><<<dim3(nblk, inst), NT, 0, st>>>(a);

@@ -46,10 +46,10 @@ struct Bump {
 struct Layout {
     // zeroed every run (contiguous)
     size_t zero_begin, frame_hist, quad_hist, quad_counts, sel_hist_a, sel_hist_b, sel_hist_c, tab_keys,
-        tab_counts, out_hist, qa,
+        tab_counts, cand_n, sel_stats, out_hist, qa,
         edge_counts, zero_end;
     size_t recipes, ctab, status, types, cast, tables, rects, q_trace, light, tile_list, tile_n, labels, ab,
-        recovered, targets, gf_gray, gf_dark, tile_lut, out, gray, cf_part, scores, best;
+        recovered, targets, cand, gf_gray, gf_dark, tile_lut, out, gray, cf_part, scores, best;
     size_t total;
 };
 
@@ -167,6 +167,8 @@ void plan_layout(uwie_engine* e) {
     L.sel_hist_c = b.take(B * nd * kSelTargets * kSelBinsC * 4);
     L.tab_keys = b.take(B * nd * kSelTargets * kSelTable * 8);
     L.tab_counts = b.take(B * nd * kSelTargets * kSelTable * 4);
+    L.cand_n = b.take(B * nd * kSelTargets * 4);
+    L.sel_stats = b.take(256);
     L.out_hist = b.take(B * S * 768 * 4);
     L.qa = b.take(B * S * sizeof(QaAccum));
     L.edge_counts = b.take(B * S * 4);
@@ -191,6 +193,7 @@ void plan_layout(uwie_engine* e) {
     L.ab = b.take(B * nd * 2 * N * 8);
     L.recovered = b.take(B * nd * N * 3 * tsz);
     L.targets = b.take(B * nd * kSelTargets * sizeof(SelTarget));
+    L.cand = b.take(B * nd * kSelTargets * (size_t)kSelListCap * tsz);
     L.gf_gray = b.take(nd ? B * N * 8 : 0);
     L.tile_lut = b.take(e->max_tiles ? B * S * kMaxTiles * 256 : 0);
     L.out = b.take(B * S * N * 3);
@@ -490,6 +493,9 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         se.sel_hist_c = e->at<unsigned>(L.sel_hist_c);
         se.tab_keys = e->at<unsigned long long>(L.tab_keys);
         se.tab_counts = e->at<unsigned>(L.tab_counts);
+        se.cand = e->at<void>(L.cand);
+        se.cand_n = e->at<unsigned>(L.cand_n);
+        se.stats = e->at<unsigned>(L.sel_stats);
         se.tables = sa.tables;
         se.status = e->at<int>(L.status);
         stage(e, st, "percentile_select", launches);
@@ -750,6 +756,7 @@ const void* uwie_engine_debug(const uwie_engine* e, const char* name, size_t* by
         {"qa", L.qa, B * S * sizeof(QaAccum)},
         {"edge_counts", L.edge_counts, B * S * 4},
         {"targets", L.targets, B * nd * kSelTargets * sizeof(SelTarget)},
+        {"sel_stats", L.sel_stats, 8},
         {"scores", L.scores, B * S * kScoreCols * 8},
     };
     for (const Item& it : items) {
