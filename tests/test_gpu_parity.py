@@ -147,6 +147,32 @@ def test_oracle_parity_odd_shapes(cuda_device, library, seed, h, w):
         assert int(res["type"][0]) == ref["type"]
 
 
+@pytest.mark.parametrize("library", ["six", "es"])
+def test_percentile_heavy_ties_take_streaming_levels(cuda_device, library):
+    """Two flat regions of ~57 000 pixels each put the low and high order statistics into level-A
+    bins that hold more members than a candidate list (kSelListCap = 32768): those targets must fall
+    back to the streaming levels B / C (+ table) and still give the reference's percentiles."""
+    h, w = 320, 400
+    rng = np.random.default_rng(11)
+    frame = np.empty((h, w, 3), np.uint8)
+    frame[:, :180] = (40, 90, 110)
+    frame[:, 180:220] = rng.integers(60, 150, size=(h, 40, 3), dtype=np.uint8)
+    frame[:, 220:] = (100, 170, 190)
+    eng = Engine(library, h, w, max_batch=1)
+    res = eng.run(torch.from_numpy(frame[None]).cuda())
+    eng.check()
+    stats = eng.debug("sel_stats", np.uint32)[:2].copy()
+    out = res["out"][0].cpu().numpy()
+    scores = res["scores"][0].cpu().numpy()
+    eng.close()
+    assert int(stats[1]) > 0, f"no target took the streaming levels: {stats}"
+    ref = o.p6_frame(frame) if library == "six" else o.p5_frame(frame)
+    d = np.abs(out.astype(np.int16) - ref["out"].astype(np.int16))
+    assert d.max() <= PIXEL_ATOL
+    assert (d != 0).mean() < 1e-3
+    assert _rel(scores, ref["scores"]).max() < SCORE_RTOL
+
+
 def test_720p_config0(cuda_device):
     """BASELINE.json configs[0]: one 1280x720 frame through the six strategies + scoring."""
     frame = synth_image(0, 720, 1280)

@@ -7,10 +7,10 @@
 //
 // Only the COUNT is wanted, so no edge map and no per-pixel label plane is ever written:
 //   1. canny_tile_kernel   64x64 tile: gradient (column march over shared memory), NMS, double
-//                          threshold -> per-row candidate / strong bit masks (64-bit words).  One warp
-//                          then floods the masks: E = candidates connected inside the tile to one of
-//                          its strong pixels (counted on the spot), P = other candidates that reach a
-//                          side shared with a neighbouring tile (pending).  Runs of P are linked by a
+//                          threshold -> per-row candidate / strong bit masks (64-bit words).  Two warps
+//                          then flood the masks side by side: E = candidates connected inside the tile
+//                          to one of its strong pixels (counted on the spot), P = other candidates that
+//                          reach a side shared with a neighbouring tile (pending).  Runs of P are linked by a
 //                          union-find in shared memory; each pending component goes to a short
 //                          per-tile list {root pixel, size}; the pixels on the tile's rim get a label
 //                          (edge / root pixel of a pending component / none) in the sparse label
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     __shared__ unsigned long long smc[TH], sms[TH];    // per tile row: candidate / strong bit masks
     __shared__ unsigned long long sme[TH], smp[TH];    // per tile row: certain edges / pending candidates
     __shared__ unsigned shist[MODE == CANNY_QUADRANTS ? 768 : 1];
-    __shared__ int s_nlist, s_any;
+    __shared__ int s_nlist;
     uint8_t (*sg)[GW] = reinterpret_cast<uint8_t (*)[GW]>(sraw);
     uint16_t (*sm)[MW] = reinterpret_cast<uint16_t (*)[MW]>(sraw + SG_BYTES);
     int* sattr = reinterpret_cast<int*>(sraw);
@@ -269,34 +269,40 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     }
     __syncthreads();      // sg / sm are dead from here on: sattr takes their place
 
-    // ---- hysteresis inside the tile: warp 0 floods the row masks (lane l owns rows 2l and 2l+1).
-    //   E = candidates connected, inside the tile, to one of its strong pixels: edges for certain
-    //   P = the other candidates that reach, inside the tile, a side shared with a neighbouring tile:
-    //       pending, they are edges iff a chain through other tiles ends at an edge
+    // ---- hysteresis inside the tile: two warps flood the row masks at the same time (lane l owns rows
+    // 2l and 2l+1).
+    //   E  (warp 0) = candidates connected, inside the tile, to one of its strong pixels: edges for certain
+    //   P' (warp 1) = candidates that reach, inside the tile, a side shared with a neighbouring tile
+    //   P = P' & ~E = pending: edges iff a chain through other tiles ends at an edge.  (A component of
+    //       the candidates lies either wholly in E or wholly outside, so the two floods are independent.)
     // Everything else is dropped here.
     const bool has_top = ty0 > 0, has_bottom = ty0 + TH < rows, has_left = tx0 > 0, has_right = tx0 + TW < cols;
     const bool any_nb = has_top || has_bottom || has_left || has_right;
-    if (tid < 32) {
-        const int r0 = 2 * tid, r1 = r0 + 1;
+    if (tid < 64) {
+        const int lane = tid & 31;
+        const int r0 = 2 * lane, r1 = r0 + 1;
         const unsigned long long c0 = smc[r0], c1 = smc[r1];
-        unsigned long long e0 = sms[r0], e1 = sms[r1];
-        flood_rows(e0, e1, c0, c1, tid);
-        unsigned cnt = (unsigned)(__popcll(e0) + __popcll(e1));
-        unsigned long long p0 = 0, p1 = 0;
-        if (any_nb) {                                                           // block-uniform
-            const unsigned long long side = (has_left ? 1ull : 0ull) | (has_right ? (1ull << 63) : 0ull);
-            const unsigned long long d0 = c0 & ~e0, d1 = c1 & ~e1;
-            p0 = d0 & ((r0 == 0 && has_top) ? ~0ull : side);
-            p1 = d1 & ((r1 == TH - 1 && has_bottom) ? ~0ull : side);
-            flood_rows(p0, p1, d0, d1, tid);
+        if (tid < 32) {
+            unsigned long long e0 = sms[r0], e1 = sms[r1];
+            flood_rows(e0, e1, c0, c1, lane);
+            sme[r0] = e0; sme[r1] = e1;
+            const unsigned cnt = warp_sum_u32((unsigned)(__popcll(e0) + __popcll(e1)));
+            if (lane == 0 && cnt) atomicAdd(&a.counts[j.out], cnt);
+        } else {
+            unsigned long long p0 = 0, p1 = 0;
+            if (any_nb) {                                                       // block-uniform
+                const unsigned long long side = (has_left ? 1ull : 0ull) | (has_right ? (1ull << 63) : 0ull);
+                p0 = c0 & ((r0 == 0 && has_top) ? ~0ull : side);
+                p1 = c1 & ((r1 == TH - 1 && has_bottom) ? ~0ull : side);
+                flood_rows(p0, p1, c0, c1, lane);
+            }
+            smp[r0] = p0; smp[r1] = p1;
         }
-        sme[r0] = e0; sme[r1] = e1; smp[r0] = p0; smp[r1] = p1;
-        cnt = warp_sum_u32(cnt);
-        if (tid == 0 && cnt) atomicAdd(&a.counts[j.out], cnt);
-        const int anyp = __any_sync(0xffffffffu, (p0 | p1) != 0ull);
-        if (tid == 0) s_any = anyp;
     }
     __syncthreads();
+    unsigned long long mine = 0ull;
+    if (tid < TH) { mine = smp[tid] & ~sme[tid]; smp[tid] = mine; }
+    const int s_any = __syncthreads_or(mine != 0ull);
 
     // ---- pending components: runs of P are the nodes of a union-find in shared memory (labels in
     // slab, sizes in sattr, both indexed by the run's first pixel)
