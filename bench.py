@@ -49,6 +49,10 @@ def parse_args():
     ap.add_argument("--e2e-frames", type=int, default=256, help="frames per e2e step (host buffers)")
     ap.add_argument("--cpu-frames", type=int, default=0, help="cpu_baseline sample size (0 = one per worker)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--entry-points", action="store_true",
+                    help="instead of the headline line: device timing of the other entry points (configs[2], "
+                         "configs[3] pieces, features79, quality_scores) with the CPU restatement beside each")
+    ap.add_argument("--out", default="", help="--entry-points: also write the JSON lines to this file")
     return ap.parse_args()
 
 
@@ -396,8 +400,28 @@ def run_native(args):
     return 0
 
 
+def run_entry_points(args):
+    """tools/bench_entry_points.py with this file's cpu_baseline leg supplying the CPU side (oracle port,
+    one frame per entry on one host core)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_entry_points as bep
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import restatement as o
+
+        def es_scored(img, name, params):
+            o.qa_total(o.es_strategy(img, name, params))
+
+        cpu = {"es_strategy_scored": es_scored, "vgg_enhance": o.vgg_enhance, "vgg_features": o.vgg_features,
+               "vgg_preprocess": o.vgg_preprocess, "features79": o.fe_all, "quality_scores": o.qa_total}
+    bep.main(cpu=cpu, out_path=args.out)
+
+
 def main():
     args = parse_args()
+    if args.entry_points:
+        run_entry_points(args)
+        return
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_native(args)

@@ -98,31 +98,36 @@ __device__ __forceinline__ int run_end(unsigned long long m, int x) {
 }
 
 // all bits of the runs of `c` that hold a bit of `s` (s within c): the carry of c + s runs up through a
-// run from its lowest seed; the bit-reversed sum runs down
-__device__ __forceinline__ unsigned long long fill_runs(unsigned long long s, unsigned long long c) {
+// run from its lowest seed; the bit-reversed sum runs down (rc = c bit-reversed, computed once per row)
+__device__ __forceinline__ unsigned long long fill_runs(unsigned long long s, unsigned long long c, unsigned long long rc) {
     const unsigned long long up = (c ^ (c + s)) & c;
-    const unsigned long long rc = __brevll(c), rs = __brevll(s);
+    const unsigned long long rs = __brevll(s);
     const unsigned long long dn = __brevll((rc ^ (rc + rs)) & rc);
     return up | dn | s;
 }
+__device__ __forceinline__ unsigned long long dilate3(unsigned long long m) { return m | (m << 1) | (m >> 1); }
 
 // 8-connected flood of the seeds (e0, e1) inside the candidates (c0, c1) of a 64-row tile held by one
 // warp, lane l owning rows 2l and 2l+1; seeds must lie inside the candidates.  Runs until nothing moves.
+// Within a round the rows are updated in the order 2l (from the lane above and row 2l+1), 2l+1 (from the
+// lane below and the NEW row 2l), 2l again (from the NEW row 2l+1): a front moves two rows per round in
+// either direction.
 __device__ __forceinline__ void flood_rows(unsigned long long& e0, unsigned long long& e1,
                                            unsigned long long c0, unsigned long long c1, int lane) {
-    e0 = fill_runs(e0, c0); e1 = fill_runs(e1, c1);
+    const unsigned long long rc0 = __brevll(c0), rc1 = __brevll(c1);
+    e0 = fill_runs(e0, c0, rc0); e1 = fill_runs(e1, c1, rc1);
     while (true) {
         unsigned long long up = __shfl_up_sync(0xffffffffu, e1, 1);
         unsigned long long dn = __shfl_down_sync(0xffffffffu, e0, 1);
         if (lane == 0) up = 0ull;
         if (lane == 31) dn = 0ull;
-        unsigned long long n0 = up | e1;
-        n0 = (n0 | (n0 << 1) | (n0 >> 1)) & c0 & ~e0;
-        if (n0) e0 |= fill_runs(n0, c0);
-        unsigned long long n1 = dn | e0;
-        n1 = (n1 | (n1 << 1) | (n1 >> 1)) & c1 & ~e1;
-        if (n1) e1 |= fill_runs(n1, c1);
-        if (!__any_sync(0xffffffffu, (n0 | n1) != 0ull)) break;
+        const unsigned long long n0 = dilate3(up | e1) & c0 & ~e0;
+        if (n0) e0 |= fill_runs(n0, c0, rc0);
+        const unsigned long long n1 = dilate3(dn | e0) & c1 & ~e1;
+        if (n1) e1 |= fill_runs(n1, c1, rc1);
+        const unsigned long long m0 = dilate3(e1) & c0 & ~e0;
+        if (m0) e0 |= fill_runs(m0, c0, rc0);
+        if (!__any_sync(0xffffffffu, (n0 | n1 | m0) != 0ull)) break;
     }
 }
 
