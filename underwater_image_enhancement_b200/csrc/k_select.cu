@@ -4,14 +4,20 @@
 // np.percentile(method='linear') needs the order statistics k and k+1.  They are found exactly by a
 // most-significant-digit radix selection over key = floor(x * 2^31) (k_arith.cuh: monotone, uniform
 // in value, exact), cut into digits of 11 / 11 / 10 bits:
-//   level A  histogram of key >> 21, accumulated inside gf_recover_kernel (no extra pass)
-//   level B  one streaming read: members of each target's A bin, by their next 11 bits
-//   level C  one streaming read: members of each target's A.B bin, by their last 10 bits
-// After level C a float32 value >= 2^-8 is known exactly (key * 2^-31).  Values that can share a
-// key (float64 data; float32 below 2^-8) are told apart by a small hash table of (bit pattern, count)
-// filled in one more streaming read that exits at once when no target needs it.
+//   level A  histogram of key >> 21, accumulated inside gf_recover_kernel (no extra pass); its first and
+//            last bins hold nothing but exact zeros / exact ones (the frame is clipped to [0, 1])
+//   level B  one streaming read: every member of a target's A bin appends its bit pattern to that
+//            target's candidate list (kSelListCap entries) and counts in a histogram of its next 11 bits
+//   lists    sel_small_kernel: the order statistic inside the list by a radix selection over the bit
+//            patterns (8-bit digits) - no further read of the frame.  This is the normal end.
+// Only a target whose A bin held more members than a list goes on:
+//   level C  one streaming read: members of the target's A.B bin, by their last 10 bits
+//   After level C a float32 value >= 2^-8 is known exactly (key * 2^-31).  Values that can share a
+//   key (float64 data; float32 below 2^-8) are told apart by a small hash table of (bit pattern, count)
+//   filled in one more streaming read that exits at once when no target needs it.
 // Heavy ties are the normal case, not a corner case: every pixel whose channel byte equals the
-// airlight's byte recovers to exactly A_c, whatever its transmission - hence counts, not lists.
+// airlight's byte recovers to exactly A_c, whatever its transmission - hence the route through
+// counts (levels B / C, table) stays for the bins a list cannot hold.
 // Because a level-A bin is 1/1024 of the value range, few elements match a target after level A;
 // the streaming passes therefore test one shared-memory byte per element (does my A bin hold any
 // target of my channel?) and only the rare hits do warp-aggregated global atomics.
