@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--e2e-frames", type=int, default=256, help="frames per e2e step (host buffers)")
     ap.add_argument("--cpu-frames", type=int, default=0, help="cpu_baseline sample size (0 = one per worker)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="N > 1: do not pin ranks to their GPU's NUMA node")
     ap.add_argument("--entry-points", action="store_true",
                     help="instead of the headline line: device timing of the other entry points (configs[2], "
                          "configs[3] pieces, features79, quality_scores) with the CPU restatement beside each")
@@ -206,6 +207,36 @@ def stage_alg_bytes(library: str):
     }
 
 
+def bind_to_gpu_numa(local):
+    """Pin this rank (and the pinned host buffers it allocates afterwards) to the CPUs of its GPU's NUMA
+    node, so that the host<->device copies of the e2e arm do not cross the socket interconnect when several
+    ranks share the box.  Best effort: returns a description, or None when the topology cannot be read."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            tok = vis.split(",")[local].strip()
+            h = pynvml.nvmlDeviceGetHandleByUUID(tok) if tok.startswith("GPU-") else pynvml.nvmlDeviceGetHandleByIndex(int(tok))
+        else:
+            h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        path = "/sys/bus/pci/devices/" + bus.lower()[-12:]
+        node = int(open(path + "/numa_node").read())
+        cpus = set()
+        for part in open(path + "/local_cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"node": node, "cpus": len(cpus)}
+    except Exception:                                                              # noqa: BLE001
+        return None
+
+
 def run_native(args):
     import torch
     import torch.distributed as dist
@@ -219,6 +250,8 @@ def run_native(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py (native arm) needs a CUDA device: there is no CPU fallback")
+    numa = bind_to_gpu_numa(local) if (world > 1 and not args.no_numa_bind) else None
+    print(f"[bench] rank {rank} numa binding: {numa}", file=sys.stderr, flush=True)
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
     if world > 1:
@@ -379,7 +412,8 @@ def run_native(args):
                    "library": args.library, "frames_per_gpu_per_step": B, "chunk": chunk,
                    "distinct_frames": distinct, "strategies": S, "lanes": lanes,
                    "l2": f"inputs {B * NPIX * 3 / 1e6:.0f} MB + outputs {B * S * NPIX * 3 / 1e6:.0f} MB per step exceed the 126 MB L2; no flush needed",
-                   "parallelism": f"image-index sharding x{world}, NCCL all-gather of score records"},
+                   "parallelism": f"image-index sharding x{world}, NCCL all-gather of score records",
+                   "numa_bind": numa},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "frames_per_step": ne, "chunk": e2e_chunk, "api": "uwie_enhance_score_host (C ABI, pinned host buffers)",
                 "matches_device_path": bool(same)},

@@ -29,7 +29,9 @@ namespace {
 
 constexpr int TH = kCannyTile, TW = kCannyTile;   // 64 x 64: one 64-bit mask per tile row
 constexpr int NT = 256;
-constexpr int GW = TW + 4, GH = TH + 4;           // gray tile with a 2-pixel halo
+constexpr int GL = TW + 4, GH = TH + 4;           // gray tile with a 2-pixel halo (logical width)
+constexpr int GPAD = 2, GW = GL + 2 * GPAD;       // stored with 2 more columns either side: tile column -4 is byte 0 of a row,
+                                                  // so an interior tile copies aligned 32-bit words straight in
 constexpr int MW = TW + 2, MH = TH + 2;           // magnitude tile with a 1-pixel halo
 constexpr int SG_BYTES = (GH * GW + 15) & ~15;
 constexpr int LABEL_FLAG = 0x40000000;
@@ -167,13 +169,13 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         const CastTables* ct = a.cast + j.img;
         for (int i = tid; i < 768; i += NT) shist[i] = 0;
         __syncthreads();
-        for (int i = tid; i < GH * GW; i += NT) {
-            const int ly = i / GW, lx = i - ly * GW;
+        for (int i = tid; i < GH * GL; i += NT) {
+            const int ly = i / GL, lx = i - ly * GL;
             const int ry = ty0 + ly - 2, rx = tx0 + lx - 2;
             const int y = j.y0 + clamp_idx(ry, rows), x = j.x0 + clamp_idx(rx, cols);
             const uint8_t* p = frame + ((size_t)y * a.W + x) * 3;
             const int r0 = p[0], g0 = p[1], b0 = p[2];
-            sg[ly][lx] = (uint8_t)gray_q15(ct->curq[0][r0], ct->curq[1][g0], ct->curq[2][b0]);
+            sg[ly][GPAD + lx] = (uint8_t)gray_q15(ct->curq[0][r0], ct->curq[1][g0], ct->curq[2][b0]);
             const bool inner = ly >= 2 && ly < TH + 2 && lx >= 2 && lx < TW + 2 && ry < rows && rx < cols;
             if (inner) {
                 atomicAdd(&shist[r0], 1u);
@@ -185,25 +187,17 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         const uint8_t* gplane = a.gray + (size_t)j.plane * npix;
         const bool word_ok = (a.W & 3) == 0 && ty0 >= 2 && ty0 + TH + 2 <= rows && tx0 >= 4 && tx0 + TW + 4 <= cols;
         if (word_ok) {
-            // interior tile: 18 aligned 32-bit words cover columns tx0-4 .. tx0+TW+3; the halo needs
-            // bytes 2,3 of the first word and bytes 0,1 of the last
+            // interior tile: 18 aligned 32-bit words cover columns tx0-4 .. tx0+TW+3 = bytes 0 .. GW-1 of a row
             for (int i = tid; i < GH * 18; i += NT) {
                 const int ly = i / 18, wx = i - ly * 18;
-                const unsigned v = *reinterpret_cast<const unsigned*>(gplane + (size_t)(ty0 + ly - 2) * a.W + tx0 - 4 + wx * 4);
-                const int lx = wx * 4 - 2;     // tile column of byte 0 of this word
-                if (wx == 0) { sg[ly][0] = (uint8_t)(v >> 16); sg[ly][1] = (uint8_t)(v >> 24); }
-                else if (wx == 17) { sg[ly][lx] = (uint8_t)v; sg[ly][lx + 1] = (uint8_t)(v >> 8); }
-                else {
-                    // lx = 2 mod 4: two 16-bit stores
-                    *reinterpret_cast<uint16_t*>(&sg[ly][lx]) = (uint16_t)v;
-                    *reinterpret_cast<uint16_t*>(&sg[ly][lx + 2]) = (uint16_t)(v >> 16);
-                }
+                *reinterpret_cast<unsigned*>(&sg[ly][wx * 4]) =
+                    *reinterpret_cast<const unsigned*>(gplane + (size_t)(ty0 + ly - 2) * a.W + tx0 - 4 + wx * 4);
             }
         } else {
-            for (int i = tid; i < GH * GW; i += NT) {
-                const int ly = i / GW, lx = i - ly * GW;
+            for (int i = tid; i < GH * GL; i += NT) {
+                const int ly = i / GL, lx = i - ly * GL;
                 const int y = clamp_idx(ty0 + ly - 2, rows), x = clamp_idx(tx0 + lx - 2, cols);
-                sg[ly][lx] = gplane[(size_t)y * a.W + x];
+                sg[ly][GPAD + lx] = gplane[(size_t)y * a.W + x];
             }
         }
     }
@@ -222,13 +216,15 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
             const bool col_in = rx >= 0 && rx < cols;
             int h1a, h1b, h2a, h2b;
             {
-                const int g0 = sg[my0][mx], g1 = sg[my0][mx + 1], g2 = sg[my0][mx + 2];
+                const uint8_t* r0p = &sg[my0][GPAD + mx];
+                const int g0 = r0p[0], g1 = r0p[1], g2 = r0p[2];
                 h1a = g2 - g0; h2a = g0 + 2 * g1 + g2;
-                const int k0 = sg[my0 + 1][mx], k1 = sg[my0 + 1][mx + 1], k2 = sg[my0 + 1][mx + 2];
+                const int k0 = r0p[GW], k1 = r0p[GW + 1], k2 = r0p[GW + 2];
                 h1b = k2 - k0; h2b = k0 + 2 * k1 + k2;
             }
             for (int my = my0; my < my1; ++my) {
-                const int g0 = sg[my + 2][mx], g1 = sg[my + 2][mx + 1], g2 = sg[my + 2][mx + 2];
+                const uint8_t* rp = &sg[my + 2][GPAD + mx];
+                const int g0 = rp[0], g1 = rp[1], g2 = rp[2];
                 const int h1c = g2 - g0, h2c = g0 + 2 * g1 + g2;
                 const int dx = h1a + 2 * h1b + h1c, dy = h2c - h2a;
                 h1a = h1b; h1b = h1c; h2a = h2b; h2b = h2c;
