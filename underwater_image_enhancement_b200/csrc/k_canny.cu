@@ -40,7 +40,6 @@ constexpr int LAB_NONE = -1, LAB_EDGE = -2;       // rim labels that are not a p
 constexpr int RIM = 2 * TW + 2 * (TH - 2);
 
 static_assert(TW == 64, "a tile row is one 64-bit mask");
-static_assert(SG_BYTES + MH * MW * 2 <= TH * TW * 4, "phase-1 buffers alias the attribute array");
 
 struct Job {
     int y0, y1, x0, x1;   // rectangle inside the plane, empty when y0 >= y1
@@ -84,6 +83,33 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b) {
         b = uf_find((volatile int*)L, b);
         if (a < b) { const int old = atomicMin(&L[b], a); done = (old == b); b = old; }
         else if (b < a) { const int old = atomicMin(&L[a], b); done = (old == a); a = old; }
+        else done = true;
+    } while (!done);
+}
+
+// ---- union-find of the pending runs of ONE tile, in shared memory.  A node is a run, named by its row and
+// the pair of columns its first pixel lies in (two runs cannot start in the same pair): row * 32 + (x >> 1).
+// A word holds label << 16 | size: atomicMin orders by label, and once the links are final the sizes are
+// added into the low half of the root's word (a component has at most 4096 pixels).
+__device__ __forceinline__ int run_node(int row, int x) { return row * 32 + (x >> 1); }
+// column of the first pixel of node `n`, given the pending mask of its row
+__device__ __forceinline__ int node_column(unsigned long long rowmask, int n) {
+    const int xx = 2 * (n & 31);
+    const unsigned long long starts = rowmask & ~(rowmask << 1);
+    return ((starts >> xx) & 1ull) ? xx : xx + 1;
+}
+__device__ __forceinline__ int suf_find(volatile int* L, int x) {
+    int l;
+    while ((l = (L[x] >> 16)) != x) x = l;
+    return x;
+}
+__device__ __forceinline__ void suf_union(int* L, int a, int b) {
+    bool done;
+    do {
+        a = suf_find(L, a);
+        b = suf_find(L, b);
+        if (a < b) { const int old = atomicMin(&L[b], a << 16) >> 16; done = (old == b); b = old; }
+        else if (b < a) { const int old = atomicMin(&L[a], b << 16) >> 16; done = (old == a); a = old; }
         else done = true;
     } while (!done);
 }
@@ -149,15 +175,14 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     const int ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
     if (ty0 >= rows || tx0 >= cols) return;
 
-    __shared__ __align__(16) unsigned char sraw[TH * TW * 4];
-    __shared__ int slab[TH * TW];
+    __shared__ __align__(16) unsigned char sraw[SG_BYTES + ((MH * MW * 2 + 15) & ~15)];
+    __shared__ int slab[TH * 32];                      // pending runs: label << 16 | size, see run_node
     __shared__ unsigned long long smc[TH], sms[TH];    // per tile row: candidate / strong bit masks
     __shared__ unsigned long long sme[TH], smp[TH];    // per tile row: certain edges / pending candidates
     __shared__ unsigned shist[MODE == CANNY_QUADRANTS ? 768 : 1];
     __shared__ int s_nlist;
     uint8_t (*sg)[GW] = reinterpret_cast<uint8_t (*)[GW]>(sraw);
     uint16_t (*sm)[MW] = reinterpret_cast<uint16_t (*)[MW]>(sraw + SG_BYTES);
-    int* sattr = reinterpret_cast<int*>(sraw);
 
     const int tid = threadIdx.x;
     const size_t npix = (size_t)a.H * a.W;
@@ -268,7 +293,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
             reinterpret_cast<unsigned*>(sms)[ly * 2 + (lx >> 5)] = mst;
         }
     }
-    __syncthreads();      // sg / sm are dead from here on: sattr takes their place
+    __syncthreads();
 
     // ---- hysteresis inside the tile: two warps flood the row masks at the same time (lane l owns rows
     // 2l and 2l+1).
@@ -305,8 +330,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     if (tid < TH) { mine = smp[tid] & ~sme[tid]; smp[tid] = mine; }
     const int s_any = __syncthreads_or(mine != 0ull);
 
-    // ---- pending components: runs of P are the nodes of a union-find in shared memory (labels in
-    // slab, sizes in sattr, both indexed by the run's first pixel)
+    // ---- pending components: runs of P are the nodes of a union-find in shared memory (slab)
     const int slot = tile_slot();
     int* lab = a.labels + (size_t)j.plane * npix;
     if (s_any) {                                                                // block-uniform
@@ -314,9 +338,10 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         const bool rowt = tid < TH;
         const unsigned long long R = rowt ? smp[tid] : 0ull;
         const unsigned long long U = (rowt && tid > 0) ? smp[tid - 1] : 0ull;
-        for (unsigned long long m = R; m;) {                                    // nodes = first pixels of the runs
+        for (unsigned long long m = R; m;) {                                    // nodes
             const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
-            slab[tid * TW + s0] = tid * TW + s0; sattr[tid * TW + s0] = 0;
+            const int n = run_node(tid, s0);
+            slab[n] = n << 16;
             m &= e0 >= 64 ? 0ull : (~0ull << e0);
         }
         __syncthreads();
@@ -329,25 +354,26 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
             for (unsigned long long t = U & hi & lo; t;) {
                 const int b0 = __ffsll((long long)t) - 1;
                 const int ue = run_end(U, b0);
-                uf_union(slab, tid * TW + s0, (tid - 1) * TW + run_start(U, b0));
+                suf_union(slab, run_node(tid, s0), run_node(tid - 1, run_start(U, b0)));
                 t &= ue >= 64 ? 0ull : (~0ull << ue);
             }
         }
         __syncthreads();
-        for (unsigned long long m = R; m;) {                                    // component sizes
+        for (unsigned long long m = R; m;) {                                    // component sizes, into the roots' low halves
             const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
             m &= e0 >= 64 ? 0ull : (~0ull << e0);
-            atomicAdd(&sattr[uf_find((volatile int*)slab, tid * TW + s0)], e0 - s0);
+            atomicAdd(&slab[suf_find((volatile int*)slab, run_node(tid, s0))], e0 - s0);
         }
         __syncthreads();
         for (unsigned long long m = R; m;) {                                    // roots -> list, nodes of the cross-tile union-find
             const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
             m &= e0 >= 64 ? 0ull : (~0ull << e0);
-            const int i = tid * TW + s0;
-            if (slab[i] != i) continue;
+            const int n = run_node(tid, s0);
+            const int w = slab[n];
+            if ((w >> 16) != n) continue;
             const int gp = (j.y0 + ty0 + tid) * a.W + (j.x0 + tx0 + s0);
             const int k = atomicAdd(&s_nlist, 1);
-            if (k < kCannyListCap) a.tile_list[(size_t)slot * kCannyListCap + k] = make_int2(gp, sattr[i]);
+            if (k < kCannyListCap) a.tile_list[(size_t)slot * kCannyListCap + k] = make_int2(gp, w & 0xffff);
             lab[gp] = gp;
         }
     }
@@ -360,8 +386,9 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
             const unsigned long long R = smp[ly];
             int v = ((sme[ly] >> lx) & 1ull) ? LAB_EDGE : LAB_NONE;
             if ((R >> lx) & 1ull) {
-                const int root = uf_find((volatile int*)slab, ly * TW + run_start(R, lx));
-                v = (j.y0 + ty0 + (root >> 6)) * a.W + (j.x0 + tx0 + (root & 63));
+                const int root = suf_find((volatile int*)slab, run_node(ly, run_start(R, lx)));
+                const int rrow = root >> 5;
+                v = (j.y0 + ty0 + rrow) * a.W + (j.x0 + tx0 + node_column(smp[rrow], root));
             }
             lab[(j.y0 + ry) * a.W + (j.x0 + rx)] = v;      // (a root on the rim gets its own index, as above)
         }
