@@ -179,10 +179,10 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     __shared__ int slab[TH * 32];                      // pending runs: label << 16 | size, see run_node
     __shared__ unsigned long long smc[TH], sms[TH];    // per tile row: candidate / strong bit masks
     __shared__ unsigned long long sme[TH], smp[TH];    // per tile row: certain edges / pending candidates
-    __shared__ unsigned shist[MODE == CANNY_QUADRANTS ? 768 : 1];
     __shared__ int s_nlist;
     uint8_t (*sg)[GW] = reinterpret_cast<uint8_t (*)[GW]>(sraw);
     uint16_t (*sm)[MW] = reinterpret_cast<uint16_t (*)[MW]>(sraw + SG_BYTES);
+    unsigned* shist = reinterpret_cast<unsigned*>(slab);   // quadrant histograms: live only while the tile is loaded
 
     const int tid = threadIdx.x;
     const size_t npix = (size_t)a.H * a.W;
@@ -227,6 +227,13 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         }
     }
     __syncthreads();
+    if (MODE == CANNY_QUADRANTS) {                   // (slab is not written again before the barriers below)
+        unsigned* gh = a.quad_hist + (size_t)j.out * 768;
+        for (int i = tid; i < 768; i += NT) {
+            const unsigned v = shist[i];
+            if (v) atomicAdd(&gh[i], v);
+        }
+    }
 
     // ---- Sobel by column march: thread = one column of the magnitude tile x one third of its rows.
     // h1 = g[x+1] - g[x-1], h2 = g[x-1] + 2 g[x] + g[x+1] per gray row; dx = h1(y-1) + 2 h1(y) + h1(y+1),
@@ -274,23 +281,29 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     // gives the candidate / strong bit masks of that half row.
     //   dir 0: m > left  && m >= right     dir 1: m > up && m >= down
     //   dir 2: m > up-right && m > down-left     dir 3: m > up-left && m > down-right
-    for (int it = 0; it < TH * TW / NT; ++it) {
-        const int i = it * NT + tid;
-        const int ly = i >> 6, lx = i & 63;
-        const uint16_t* c = &sm[ly + 1][lx + 1];
-        const int v = c[0], m = v & 0xfff;
-        bool cand = false;
-        if (m > a.low) {
-            const int dir = v >> 12;
-            const int d = (int)((((unsigned)(MW + 1) << 24) | ((MW - 1) << 16) | (MW << 8) | 1u) >> (dir * 8)) & 0xff;
-            const int mf = c[-d] & 0xfff, ms = c[d] & 0xfff;
-            cand = m > mf && m > ms - (dir < 2 ? 1 : 0);
+    // The 16 mask words of a warp stay in registers (lane `it` keeps pass `it`) and are stored once.
+    {
+        const int lane = tid & 31, warp = tid >> 5;
+        const uint16_t* c = &sm[(tid >> 6) + 1][(tid & 63) + 1];
+        const int low = a.low, high = a.high;
+        unsigned keep_c = 0u, keep_s = 0u;
+#pragma unroll
+        for (int it = 0; it < TH * TW / NT; ++it, c += (NT / TW) * MW) {
+            const int v = c[0], m = v & 0xfff;
+            bool cand = false;
+            if (m > low) {
+                const int dir = v >> 12;
+                const int d = (int)((((unsigned)(MW + 1) << 24) | ((MW - 1) << 16) | (MW << 8) | 1u) >> (dir * 8)) & 0xff;
+                const int mf = c[-d] & 0xfff, ms = c[d] & 0xfff;
+                cand = m > mf && m > ms - (dir < 2 ? 1 : 0);
+            }
+            const unsigned mc = __ballot_sync(0xffffffffu, cand);
+            const unsigned mst = __ballot_sync(0xffffffffu, cand && m > high);
+            if (lane == it) { keep_c = mc; keep_s = mst; }
         }
-        const unsigned mc = __ballot_sync(0xffffffffu, cand);
-        const unsigned mst = __ballot_sync(0xffffffffu, cand && m > a.high);
-        if ((tid & 31) == 0) {
-            reinterpret_cast<unsigned*>(smc)[ly * 2 + (lx >> 5)] = mc;
-            reinterpret_cast<unsigned*>(sms)[ly * 2 + (lx >> 5)] = mst;
+        if (lane < TH * TW / NT) {                 // pass `lane`: tile row lane * 4 + warp / 2, half warp & 1
+            reinterpret_cast<unsigned*>(smc)[lane * 8 + warp] = keep_c;
+            reinterpret_cast<unsigned*>(sms)[lane * 8 + warp] = keep_s;
         }
     }
     __syncthreads();
@@ -396,13 +409,6 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     __syncthreads();
     if (tid == 0) a.tile_n[slot] = min(s_nlist, kCannyListCap);
 
-    if (MODE == CANNY_QUADRANTS) {
-        unsigned* gh = a.quad_hist + (size_t)j.out * 768;
-        for (int i = tid; i < 768; i += NT) {
-            const unsigned v = shist[i];
-            if (v) atomicAdd(&gh[i], v);
-        }
-    }
 }
 
 // ---- pass 2 / 3 walk the rims.  One thread per rim pixel; every cross-tile pair of 8-neighbours is
