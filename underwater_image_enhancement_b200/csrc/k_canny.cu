@@ -40,6 +40,7 @@ constexpr int LAB_NONE = -1, LAB_EDGE = -2;       // rim labels that are not a p
 constexpr int RIM = 2 * TW + 2 * (TH - 2);
 
 static_assert(TW == 64, "a tile row is one 64-bit mask");
+static_assert(NT == 4 * TH, "pending runs: one thread per quarter of a tile row");
 
 struct Job {
     int y0, y1, x0, x1;   // rectangle inside the plane, empty when y0 >= y1
@@ -246,6 +247,9 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
             const int my0 = chunk * CHUNK, my1 = min(my0 + CHUNK, MH);
             const int rx = tx0 + mx - 1;
             const bool col_in = rx >= 0 && rx < cols;
+            // rows of this chunk that lie inside the rectangle: one unsigned compare per row
+            const int vlo = max(my0, 1 - ty0);
+            const unsigned vspan = col_in ? (unsigned)max(min(my1, rows - ty0 + 1) - vlo, 0) : 0u;
             int h1a, h1b, h2a, h2b;
             {
                 const uint8_t* r0p = &sg[my0][GPAD + mx];
@@ -260,10 +264,9 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
                 const int h1c = g2 - g0, h2c = g0 + 2 * g1 + g2;
                 const int dx = h1a + 2 * h1b + h1c, dy = h2c - h2a;
                 h1a = h1b; h1b = h1c; h2a = h2b; h2b = h2c;
-                const int ry = ty0 + my - 1;
                 const int ax = abs(dx), ay = abs(dy);
                 int v = 0;
-                if (col_in && ry >= 0 && ry < rows) {
+                if ((unsigned)(my - vlo) < vspan) {
                     const int ys = ay << 15, tg22x = ax * 13573;
                     int dir;
                     if (ys < tg22x) dir = 0;
@@ -347,44 +350,41 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     const int slot = tile_slot();
     int* lab = a.labels + (size_t)j.plane * npix;
     if (s_any) {                                                                // block-uniform
-        // P is sparse: one thread per tile row walks the runs of its 64-bit mask
-        const bool rowt = tid < TH;
-        const unsigned long long R = rowt ? smp[tid] : 0ull;
-        const unsigned long long U = (rowt && tid > 0) ? smp[tid - 1] : 0ull;
-        for (unsigned long long m = R; m;) {                                    // nodes
-            const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
-            const int n = run_node(tid, s0);
+        // P is sparse: a thread owns the runs that START in one 16-column quarter of a tile row, so the
+        // walks are short and all eight warps share them
+        const int row = tid >> 2;
+        const unsigned long long R = smp[row];
+        const unsigned long long U = row > 0 ? smp[row - 1] : 0ull;
+        const unsigned long long mystarts = R & ~(R << 1) & (0xffffull << (16 * (tid & 3)));
+        for (unsigned long long m = mystarts; m; m &= m - 1) {                  // nodes
+            const int n = run_node(row, __ffsll((long long)m) - 1);
             slab[n] = n << 16;
-            m &= e0 >= 64 ? 0ull : (~0ull << e0);
         }
         __syncthreads();
-        for (unsigned long long m = R; m;) {                                    // link to the runs of the row above
+        for (unsigned long long m = mystarts; m; m &= m - 1) {                  // link to the runs of the row above
             const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
-            m &= e0 >= 64 ? 0ull : (~0ull << e0);
             // 8-connectivity: columns s0-1 .. e0 of the row above
             const unsigned long long hi = e0 >= 63 ? ~0ull : ((1ull << (e0 + 1)) - 1ull);
             const unsigned long long lo = s0 == 0 ? ~0ull : (~0ull << (s0 - 1));
             for (unsigned long long t = U & hi & lo; t;) {
                 const int b0 = __ffsll((long long)t) - 1;
                 const int ue = run_end(U, b0);
-                suf_union(slab, run_node(tid, s0), run_node(tid - 1, run_start(U, b0)));
+                suf_union(slab, run_node(row, s0), run_node(row - 1, run_start(U, b0)));
                 t &= ue >= 64 ? 0ull : (~0ull << ue);
             }
         }
         __syncthreads();
-        for (unsigned long long m = R; m;) {                                    // component sizes, into the roots' low halves
+        for (unsigned long long m = mystarts; m; m &= m - 1) {                  // component sizes, into the roots' low halves
             const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
-            m &= e0 >= 64 ? 0ull : (~0ull << e0);
-            atomicAdd(&slab[suf_find((volatile int*)slab, run_node(tid, s0))], e0 - s0);
+            atomicAdd(&slab[suf_find((volatile int*)slab, run_node(row, s0))], e0 - s0);
         }
         __syncthreads();
-        for (unsigned long long m = R; m;) {                                    // roots -> list, nodes of the cross-tile union-find
-            const int s0 = __ffsll((long long)m) - 1, e0 = run_end(R, s0);
-            m &= e0 >= 64 ? 0ull : (~0ull << e0);
-            const int n = run_node(tid, s0);
+        for (unsigned long long m = mystarts; m; m &= m - 1) {                  // roots -> list, nodes of the cross-tile union-find
+            const int s0 = __ffsll((long long)m) - 1;
+            const int n = run_node(row, s0);
             const int w = slab[n];
             if ((w >> 16) != n) continue;
-            const int gp = (j.y0 + ty0 + tid) * a.W + (j.x0 + tx0 + s0);
+            const int gp = (j.y0 + ty0 + row) * a.W + (j.x0 + tx0 + s0);
             const int k = atomicAdd(&s_nlist, 1);
             if (k < kCannyListCap) a.tile_list[(size_t)slot * kCannyListCap + k] = make_int2(gp, w & 0xffff);
             lab[gp] = gp;
