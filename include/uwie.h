@@ -106,12 +106,21 @@ int uwie_enhance_score(uwie_engine* e, const uint8_t* frames_dev, int batch,
 
 /* Same call with HOST buffers (any count of frames, processed in chunks of max_batch): copies the
  * frames to the device, runs, copies the requested results back, synchronises.  Pinned host
- * memory makes the copies asynchronous with respect to the kernels of the neighbouring chunk. */
+ * memory makes the copies asynchronous with respect to the kernels of the neighbouring chunk.
+ * The call allocates nothing: uwie_engine_host_prepare must have been called once with
+ * max_count >= count and the want_* flags of the outputs that will be asked for (it owns the
+ * double-buffered device slots, the pinned landing zone of the small results, the copy streams
+ * and, when max_count > max_batch, the second lane's engine); otherwise UWIE_ERR_ARG.
+ * This is the loop body of main.py:88-155 / six_stadigy.py:392-447 without the file I/O. */
+int uwie_engine_host_prepare(uwie_engine* e, int max_count, int want_all, int want_best);
 int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int count,
                             uint8_t* out_all_host, uint8_t* out_best_host, double* scores_host,
                             int32_t* best_host, int32_t* type_host, float* light_host, void* stream);
 
-/* Sticky device-side status of the engine (synchronises `stream`): 0 or a negative uwie_status. */
+/* Device-side status of the engine's calls since the last check (synchronises `stream`, read-and-clear):
+ * 0 or a negative uwie_status.  uwie_enhance_score is asynchronous and cannot report a device-side
+ * failure itself (an exact percentile selection that overflowed, UWIE_ERR_SELECT): callers of the
+ * device entry point must check before they trust the results; the host entry point does it itself. */
 int uwie_engine_check(uwie_engine* e, void* stream);
 
 /* Kernels launched by the last uwie_enhance_score call on this engine. */

@@ -15,7 +15,8 @@ OK, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_SELECT = 0, -1, -2, -3, -4
 
 # every symbol include/uwie.h declares (tests check that the library exports all of them)
 EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_bytes", "uwie_engine_create",
-           "uwie_engine_destroy", "uwie_enhance_score", "uwie_enhance_score_host", "uwie_engine_check",
+           "uwie_engine_destroy", "uwie_enhance_score", "uwie_engine_host_prepare", "uwie_enhance_score_host",
+           "uwie_engine_check",
            "uwie_engine_last_launches", "uwie_engine_debug", "uwie_engine_profile",
            "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_features_u8",
            "uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32", "uwie_features79_workspace_bytes",
@@ -73,6 +74,8 @@ def load() -> C.CDLL:
     lib.uwie_enhance_score.restype = C.c_int
     lib.uwie_enhance_score_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7
     lib.uwie_enhance_score_host.restype = C.c_int
+    lib.uwie_engine_host_prepare.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+    lib.uwie_engine_host_prepare.restype = C.c_int
     lib.uwie_engine_check.argtypes = [C.c_void_p, C.c_void_p]
     lib.uwie_engine_check.restype = C.c_int
     lib.uwie_engine_last_launches.argtypes = [C.c_void_p]

@@ -582,6 +582,8 @@ int uwie_engine_check(uwie_engine* e, void* stream) {
     CU(cudaMemcpyAsync(&status, e->ws + e->L.status, sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     if (status) {
+        // read-and-clear: the failure is reported once, for the calls since the last check
+        CU(cudaMemsetAsync(e->ws + e->L.status, 0, sizeof(int), st));
         char buf[128];
         std::snprintf(buf, sizeof(buf), "percentile selection failed on the device (status bits %d)", status);
         return fail(UWIE_ERR_SELECT, buf);
@@ -594,12 +596,13 @@ int uwie_engine_check(uwie_engine* e, void* stream) {
 // while the kernels of chunk i run on the caller's stream (the workspace is single, so kernels of
 // different chunks never overlap each other).  With pinned host buffers the copies are truly
 // asynchronous; with pageable ones CUDA stages them and the result is the same, only slower.
-int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int count, uint8_t* out_all_host,
-                            uint8_t* out_best_host, double* scores_host, int32_t* best_host,
-                            int32_t* type_host, float* light_host, void* stream) {
-    if (!e || !frames_host) return fail(UWIE_ERR_ARG, "null engine or frames");
-    if (count < 1) return fail(UWIE_ERR_ARG, "count must be positive");
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
+//
+// Every allocation of that pipeline (device slots, the pinned landing zone of the small results,
+// streams, events and the second lane's engine) happens in uwie_engine_host_prepare; the call
+// itself allocates nothing and fails with UWIE_ERR_ARG when the engine was not prepared for it.
+int uwie_engine_host_prepare(uwie_engine* e, int max_count, int want_all, int want_best) {
+    if (!e) return fail(UWIE_ERR_ARG, "null engine");
+    if (max_count < 1) return fail(UWIE_ERR_ARG, "max_count must be positive");
     const size_t N = (size_t)e->H * e->W, S = e->S, B = e->B;
     uwie_engine::HostPipe& hp = e->pipe;
     if (!hp.ready) {
@@ -610,29 +613,24 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
             CU(cudaEventCreateWithFlags(&hp.ev_run[k], cudaEventDisableTiming));
             CU(cudaEventCreateWithFlags(&hp.ev_out[k], cudaEventDisableTiming));
             CU(cudaMalloc(&hp.frames[k], B * N * 3));
-            CU(cudaMalloc(&hp.best_img[k], B * N * 3));
             CU(cudaMalloc(&hp.small[k], B * (S * kScoreCols * 8 + 4 + 4 + 12) + 256));
         }
         CU(cudaEventCreateWithFlags(&hp.ev_start, cudaEventDisableTiming));
         hp.ready = true;
     }
-    // out_all of both slots is allocated only if somebody asks for it (it is S times a chunk)
-    if (out_all_host && !hp.out_all[0]) {
+    if (want_best && !hp.best_img[0])
+        for (int k = 0; k < 2; ++k) CU(cudaMalloc(&hp.best_img[k], B * N * 3));
+    if (want_all && !hp.out_all[0])                        // S times a chunk: only if somebody asks for it
         for (int k = 0; k < 2; ++k) CU(cudaMalloc(&hp.out_all[k], B * S * N * 3));
-    }
     const size_t rec_bytes = S * kScoreCols * 8 + 4 + 4 + 12;
-    if (hp.h_small_frames < (size_t)count) {
+    if (hp.h_small_frames < (size_t)max_count) {
         if (hp.h_small) cudaFreeHost(hp.h_small);
         hp.h_small = nullptr; hp.h_small_frames = 0;
-        CU(cudaMallocHost(&hp.h_small, (size_t)count * rec_bytes + 64));
-        hp.h_small_frames = count;
+        CU(cudaMallocHost(&hp.h_small, (size_t)max_count * rec_bytes + 64));
+        hp.h_small_frames = max_count;
     }
-    double* p_scores = reinterpret_cast<double*>(hp.h_small);
-    int32_t* p_best = reinterpret_cast<int32_t*>(p_scores + (size_t)count * S * kScoreCols);
-    int32_t* p_types = p_best + count;
-    float* p_light = reinterpret_cast<float*>(p_types + count);
     // second lane (see HostPipe): only worth its workspace when there is more than one chunk
-    if (count > (int)B && !hp.twin && !hp.twin_failed && !e->prof_on && !std::getenv("UWIE_HOST_ONE_LANE")) {
+    if (max_count > (int)B && !hp.twin && !hp.twin_failed && !std::getenv("UWIE_HOST_ONE_LANE")) {
         if (uwie_engine_create(&hp.twin, &e->pub_lib, e->pub_strategies.data(), (int)S, (int)B, e->H, e->W, nullptr, 0) != UWIE_OK ||
             cudaStreamCreateWithFlags(&hp.s_run2, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreateWithFlags(&hp.ev_twin, cudaEventDisableTiming) != cudaSuccess) {
@@ -641,6 +639,25 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
             hp.twin_failed = true;                   // e.g. no memory for a second workspace: one lane it is
         }
     }
+    return UWIE_OK;
+}
+
+int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int count, uint8_t* out_all_host,
+                            uint8_t* out_best_host, double* scores_host, int32_t* best_host,
+                            int32_t* type_host, float* light_host, void* stream) {
+    if (!e || !frames_host) return fail(UWIE_ERR_ARG, "null engine or frames");
+    if (count < 1) return fail(UWIE_ERR_ARG, "count must be positive");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t N = (size_t)e->H * e->W, S = e->S, B = e->B;
+    uwie_engine::HostPipe& hp = e->pipe;
+    if (!hp.ready || hp.h_small_frames < (size_t)count || (out_all_host && !hp.out_all[0]) ||
+        (out_best_host && !hp.best_img[0]))
+        return fail(UWIE_ERR_ARG, "uwie_enhance_score_host: call uwie_engine_host_prepare(engine, max_count, want_all, "
+                                  "want_best) first (the call itself allocates nothing)");
+    double* p_scores = reinterpret_cast<double*>(hp.h_small);
+    int32_t* p_best = reinterpret_cast<int32_t*>(p_scores + (size_t)count * S * kScoreCols);
+    int32_t* p_types = p_best + count;
+    float* p_light = reinterpret_cast<float*>(p_types + count);
     const bool two_lanes = hp.twin && !e->prof_on && count > (int)B;
     // the copy streams must not start before work already queued on the caller's stream
     CU(cudaEventRecord(hp.ev_start, st));

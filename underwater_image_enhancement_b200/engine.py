@@ -134,10 +134,22 @@ class Engine:
 
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         with torch.cuda.device(self.device):
+            self.host_prepare(n, out_all is not None, out_best is not None)
             _lib.check(self._lib.uwie_enhance_score_host(self._h, hp(frames), n, hp(out_all), hp(out_best),
                                                          hp(scores), hp(best), hp(types), hp(light), stream))
         return {"out": out_all, "best_out": out_best, "scores": scores, "best": best, "type": types,
                 "light": light}
+
+    def host_prepare(self, max_count: int, want_all: bool = True, want_best: bool = False):
+        """Allocate what run_host needs for up to `max_count` frames per call (uwie_engine_host_prepare):
+        the host entry point itself allocates nothing.  Idempotent; run_host calls it on demand."""
+        key = (int(max_count), bool(want_all), bool(want_best))
+        have = getattr(self, "_host_ready", (0, False, False))
+        if have[0] >= key[0] and (have[1] or not key[1]) and (have[2] or not key[2]):
+            return
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.uwie_engine_host_prepare(self._h, key[0], int(key[1]), int(key[2])))
+        self._host_ready = (max(have[0], key[0]), have[1] or key[1], have[2] or key[2])
 
     # ------------------------------------------------------------------ per-stage device timing
     def profile(self, enable: bool = True):

@@ -66,6 +66,7 @@ def _run(library, frames, want_all, want_best):
                 out_all=None if out_all is None else out_all[c0:c1],
                 out_best=None if out_best is None else out_best[c0:c1],
                 scores=scores[c0:c1], best=best[c0:c1], types=types[c0:c1])
+    eng.check()     # device-side failures (percentile selection overflow) must not pass as plausible outputs
     return out_all, out_best, scores, best, types
 
 
