@@ -117,6 +117,10 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
                             uint8_t* out_all_host, uint8_t* out_best_host, double* scores_host,
                             int32_t* best_host, int32_t* type_host, float* light_host, void* stream);
 
+/* detect_image_type (six_stadigy.py:292-302) of `batch` frames on the device: 0 normal / 1 greenish / 2 bluish.
+ * Runs the channel histograms and the colour-cast set-up only.  Asynchronous on `stream`. */
+int uwie_engine_image_types(uwie_engine* e, const uint8_t* frames_dev, int batch, int32_t* type_dev, void* stream);
+
 /* Device-side status of the engine's calls since the last check (synchronises `stream`, read-and-clear):
  * 0 or a negative uwie_status.  uwie_enhance_score is asynchronous and cannot report a device-side
  * failure itself (an exact percentile selection that overflowed, UWIE_ERR_SELECT): callers of the
@@ -159,6 +163,21 @@ int uwie_vgg_enhance(const float* img_dev, int batch, int height, int width,
                      const float* l_low, const float* l_high, const float* omega, const float* gamma,
                      float* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* The same enhancement with DEVICE-resident parameters — the outputs of the parameter network, so that a batch
+ * needs no per-image host round trip (use_trained_model.py:63-66 does .cpu().item() per parameter).
+ * params_dev: float32 [4][batch] = L_low, L_high, omega, gamma rows.  clamp_ranges: apply the safety ranges of
+ * use_trained_model.py:74-79 (L_low 1..30, L_high 65..99, omega .1...9, gamma .5..3) on the device first;
+ * used_dev (may be NULL): float32 [4][batch], the values actually applied. */
+int uwie_vgg_enhance_dev(const float* img_dev, int batch, int height, int width, const float* params_dev, int clamp_ranges,
+                         float* used_dev, float* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* Backward of the enhancement for the training loops (vgg_16_UIE.py:529, deep_learning_parameters.py:281): given
+ * d loss / d out (float32 NCHW), the input image and the WORKSPACE of the forward uwie_vgg_enhance[_dev] call on the same
+ * batch (it still holds the order statistics and parameters), writes d loss / d omega and d loss / d gamma as float64
+ * [2][batch].  L_low / L_high get no gradient in the reference either (they pass through .item(), VGG:78-79). */
+int uwie_vgg_enhance_bwd(const float* img_dev, const float* grad_out_dev, int batch, int height, int width,
+                         const void* workspace_dev, size_t workspace_bytes, double* grad_params_dev, void* stream);
+
 /* extract_all_features (vgg_16_UIE.py:435-466) of uint8 RGB frames [batch][H][W][3] (the reference
  * divides by 255 first, VGG:425-433): per channel mean, std, min, max, median; overall mean, std,
  * mean of squares; zeros up to 79.  feat_dev: float32 [batch][79]. */
@@ -196,6 +215,81 @@ int uwie_quality_scores(const void* img_dev, int dtype, int batch, int height, i
 size_t uwie_features79_workspace_bytes(int batch, int height, int width);
 int uwie_features79(const uint8_t* frames_dev, int batch, int height, int width, double* feat_dev,
                     void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Per-primitive entry points: the public static methods of the reference's two
+ * EnhancementStrategies classes as stand-alone operators.  Stateless, caller-owned device memory and
+ * workspace (`*_workspace_bytes`), asynchronous on `stream` unless stated.  Float images are
+ * [H][W][3] with dtype 1 = float32, 2 = float64 (the codes of uwie_quality_scores); they need NOT be
+ * made from bytes (example_usage.py:27 feeds np.random.rand images).
+ * ------------------------------------------------------------------------------------------- */
+
+/* Transmission head on uint8 frames [batch][H][W][3] (BASELINE.json configs[2], 7 N bytes per frame):
+ * t0 = 1 - omega * min_c((v_c / 255) / (A_c + guard)) in float32, clipped to [.1, 1] when clip_t0
+ * (six_stadigy.py:170-174; enhancement_strategies.py:221-225 with clip_t0 = 0).  light_dev: float32
+ * [batch][3]; t_dev: float32 [batch][H][W]. */
+int uwie_prim_transmission_head_u8(const uint8_t* frames_dev, int batch, int height, int width, const float* light_dev,
+                                   float omega, float guard, int clip_t0, float* t_dev, void* stream);
+
+/* cv2.createCLAHE(clip_limit, (tiles_x, tiles_y)).apply on uint8 planes [batch][H][W] — the Lab L plane of
+ * enhancement_strategies.py:302-303 / six_stadigy.py:205-206 (configs[2], 2 N bytes per plane). Bit-exact. */
+size_t uwie_prim_clahe_lab_workspace_bytes(int batch, int tiles_x, int tiles_y);
+int uwie_prim_clahe_lab(const uint8_t* plane_dev, int batch, int height, int width, double clip_limit, int tiles_x,
+                        int tiles_y, uint8_t* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* cv2.equalizeHist per channel of uint8 frames [batch][H][W][3] (enhancement_strategies.py:339-343).
+ * Workspace: batch * 3840 bytes. */
+int uwie_prim_equalize_hist(const uint8_t* frames_dev, int batch, int height, int width, uint8_t* out_dev,
+                            void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* (img * 255).astype(uint8) of `count` float values (ES:298, SS:204, QA:25). */
+int uwie_prim_quantise(const void* img_dev, int dtype, size_t count, uint8_t* out_dev, void* stream);
+
+/* estimate_atmospheric_light(image, min_size=1) (ES:77-206, SS:48-165): quadtree descent on a float image;
+ * light_dev receives the (3,) pixel in the image's dtype. */
+size_t uwie_prim_atmospheric_light_workspace_bytes(int height, int width);
+int uwie_prim_atmospheric_light(const void* img_dev, int dtype, int height, int width, void* light_dev,
+                                void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* compute_Q(block) (ES:147-188, SS:115-157) of a whole float image -> one float64 on the device, and
+ * get_brightest_pixel(block) (ES:191-206, SS:159-165) -> 3 values of the image's dtype (workspace: 256 bytes). */
+size_t uwie_prim_region_score_workspace_bytes(int height, int width);
+int uwie_prim_region_score(const void* img_dev, int dtype, int height, int width, double* q_dev, void* workspace_dev,
+                           size_t workspace_bytes, void* stream);
+int uwie_prim_brightest_pixel(const void* img_dev, int dtype, int height, int width, void* light_dev, void* workspace_dev,
+                              size_t workspace_bytes, void* stream);
+
+/* guided_filter(I, p, r, eps) on float64 planes [H][W] (ES:16-46, SS:25-46); clip_01_1: clip the result to [.1, 1]. */
+size_t uwie_prim_guided_filter_workspace_bytes(int height, int width);
+int uwie_prim_guided_filter(const double* guide_dev, const double* src_dev, int height, int width, int radius, double eps,
+                            int clip_01_1, double* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* estimate_transmission(img, A, omega, r, eps) -> float64 [H][W] in [.1, 1].  light_dev: 3 values of the image's
+ * dtype.  (guard, clip_t0) = (1e-6, 1) is six_stadigy.py:167-180, (1e-10, 0) enhancement_strategies.py:209-234. */
+size_t uwie_prim_transmission_workspace_bytes(int height, int width);
+int uwie_prim_transmission(const void* img_dev, int dtype, int height, int width, const void* light_dev, double omega,
+                           int radius, double eps, double guard, int clip_t0, double* t_dev, void* workspace_dev,
+                           size_t workspace_bytes, void* stream);
+
+/* recover_image / restore_image: clip((img - A) / t + A, 0, 1) stored as out_dtype (ES:237-249 float64, SS:182-188 float32). */
+int uwie_prim_recover(const void* img_dev, int dtype, int height, int width, const double* t_dev, const void* light_dev,
+                      void* out_dev, int out_dtype, void* stream);
+
+/* color_enhancement / enhance_contrast / white_balance: per channel clip((x - p_lo) / (p_hi - p_lo + guard), 0, 1) with the
+ * exact np.percentile (ES:252-273, SS:190-219).  The image must lie in [0, 1], else UWIE_ERR_ARG.  Synchronises `stream`. */
+size_t uwie_prim_percentile_stretch_workspace_bytes(int dtype);
+int uwie_prim_percentile_stretch(const void* img_dev, int dtype, int height, int width, double lo_pct, double hi_pct,
+                                 double guard, void* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* gamma_correction: img ** exponent, clipped to [0, 1] when `clip` (ES:276-285: 1 / gamma, clip; SS:221-224: gamma, no clip). */
+int uwie_prim_gamma(const void* img_dev, int dtype, size_t count, double exponent, int clip, void* out_dev, void* stream);
+
+/* color_correction (SS:305-323): clip(img * scale3[c], 0, 1); scale3 is a HOST array. */
+int uwie_prim_scale_clip(const void* img_dev, int dtype, int height, int width, const double* scale3, void* out_dev, void* stream);
+
+/* Channel means of a float image (detect_image_type, SS:292-302): 3 float64 on the device.  Workspace: 512 bytes. */
+int uwie_prim_channel_means(const void* img_dev, int dtype, int height, int width, double* means_dev, void* workspace_dev,
+                            size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Self-test of the guided filter's branch-free float64 division and reciprocal (k_arith.cuh) against the

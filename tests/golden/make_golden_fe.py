@@ -31,10 +31,19 @@ def main():
     from underwater_image_enhancement_b200.synth import synth_image
     install_skimage_standin()
     import skimage
-    skimage.feature.local_binary_pattern = lambda image, P, R, method="default": \
-        o.sk_local_binary_pattern_uniform(image, P, R)
-    skimage.feature.graycomatrix = lambda image, distances, angles, levels, symmetric, normed: \
-        o.sk_graycomatrix(image, levels)
+    # The stand-ins restate ONE configuration of the scikit-image functions — the one feature_extraction.py:97, 107-112
+    # asks for — and refuse anything else instead of silently ignoring the arguments.
+    def local_binary_pattern(image, P, R, method="default"):
+        assert (P, R, method) == (8, 1, "uniform"), (P, R, method)
+        return o.sk_local_binary_pattern_uniform(image, P, R)
+
+    def graycomatrix(image, distances, angles, levels=None, symmetric=False, normed=False):
+        assert list(distances) == [1] and levels == 256 and symmetric is True and normed is True, (distances, levels, symmetric, normed)
+        assert np.allclose(list(angles), [0, np.pi / 4, np.pi / 2, 3 * np.pi / 4]), angles
+        return o.sk_graycomatrix(image, levels)
+
+    skimage.feature.local_binary_pattern = local_binary_pattern
+    skimage.feature.graycomatrix = graycomatrix
     skimage.feature.graycoprops = o.sk_graycoprops
     sys.path.insert(0, REF)
     import feature_extraction as fe

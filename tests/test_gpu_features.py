@@ -71,3 +71,27 @@ def test_constant_frame():
     fin = np.isfinite(want)
     assert np.array_equal(np.isfinite(got), fin)
     assert np.allclose(got[fin], want[fin], rtol=RTOL, atol=1e-5)
+
+
+def test_texture_anchors_on_device(cuda_device):
+    """The 22 texture values against expectations that do NOT come from oracle/restatement.py (tests/test_texture_anchors.py):
+    LBP histograms of constant frames derived by hand (interior code 8, edges 5, corners 3; all 8 for a black frame) and
+    GLCM statistics of a 128 x 128 frame (cv2.resize to 128 x 128 is then the identity) computed from the definition."""
+    from test_texture_anchors import glcm_by_definition, lbp_expected_constant, props_by_definition
+    h = w = 128
+    rng = np.random.default_rng(9)
+    gray = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    gray[20:60, 30:90] = 17                                               # a flat block: repeated pairs on the diagonal
+    frames = np.stack([np.zeros((h, w, 3), np.uint8), np.full((h, w, 3), 90, np.uint8),
+                       np.repeat(gray[:, :, None], 3, axis=2)])           # r = g = b -> GRAY == the value itself
+    feats = F.extract_all_features_batch(frames).cpu().numpy()[:, 35:57]
+    for i, positive in ((0, False), (1, True)):
+        codes = lbp_expected_constant(h, w, positive)
+        want = np.bincount(codes.astype(np.int64).ravel(), minlength=10) / float(h * w)   # density with unit bins
+        assert np.allclose(feats[i, :10], want, rtol=1e-12, atol=1e-15), i
+    P = glcm_by_definition(gray, 256)
+    props = props_by_definition(P)
+    want = []
+    for k in ("contrast", "dissimilarity", "homogeneity", "energy", "correlation", "ASM"):
+        want += [np.mean(props[k]), np.std(props[k])]
+    assert np.allclose(feats[2, 10:], want, rtol=1e-9, atol=1e-12), np.abs(feats[2, 10:] - np.asarray(want)).max()

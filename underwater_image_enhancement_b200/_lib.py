@@ -16,11 +16,18 @@ OK, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_SELECT = 0, -1, -2, -3, -4
 # every symbol include/uwie.h declares (tests check that the library exports all of them)
 EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_bytes", "uwie_engine_create",
            "uwie_engine_destroy", "uwie_enhance_score", "uwie_engine_host_prepare", "uwie_enhance_score_host",
-           "uwie_engine_check",
+           "uwie_engine_image_types", "uwie_engine_check",
            "uwie_engine_last_launches", "uwie_engine_debug", "uwie_engine_profile",
-           "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_features_u8",
+           "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_enhance_dev", "uwie_vgg_enhance_bwd", "uwie_vgg_features_u8",
            "uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32", "uwie_features79_workspace_bytes",
-           "uwie_features79", "uwie_quality_workspace_bytes", "uwie_quality_scores", "uwie_selftest_division")
+           "uwie_features79", "uwie_quality_workspace_bytes", "uwie_quality_scores", "uwie_selftest_division",
+           "uwie_prim_transmission_head_u8", "uwie_prim_clahe_lab_workspace_bytes", "uwie_prim_clahe_lab",
+           "uwie_prim_equalize_hist", "uwie_prim_quantise", "uwie_prim_atmospheric_light_workspace_bytes",
+           "uwie_prim_atmospheric_light", "uwie_prim_guided_filter_workspace_bytes", "uwie_prim_guided_filter",
+           "uwie_prim_transmission_workspace_bytes", "uwie_prim_transmission", "uwie_prim_recover",
+           "uwie_prim_percentile_stretch_workspace_bytes", "uwie_prim_percentile_stretch", "uwie_prim_gamma",
+           "uwie_prim_scale_clip", "uwie_prim_channel_means", "uwie_prim_region_score_workspace_bytes",
+           "uwie_prim_region_score", "uwie_prim_brightest_pixel")
 FEATURES = 79
 VGG_FEATURES = 79
 STAGE_NAME_LEN = 32
@@ -74,6 +81,8 @@ def load() -> C.CDLL:
     lib.uwie_enhance_score.restype = C.c_int
     lib.uwie_enhance_score_host.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 7
     lib.uwie_enhance_score_host.restype = C.c_int
+    lib.uwie_engine_image_types.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    lib.uwie_engine_image_types.restype = C.c_int
     lib.uwie_engine_host_prepare.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
     lib.uwie_engine_host_prepare.restype = C.c_int
     lib.uwie_engine_check.argtypes = [C.c_void_p, C.c_void_p]
@@ -93,6 +102,12 @@ def load() -> C.CDLL:
     lib.uwie_vgg_enhance.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, fp, fp, fp, fp, C.c_void_p, C.c_void_p,
                                      C.c_size_t, C.c_void_p]
     lib.uwie_vgg_enhance.restype = C.c_int
+    lib.uwie_vgg_enhance_dev.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.uwie_vgg_enhance_dev.restype = C.c_int
+    lib.uwie_vgg_enhance_bwd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p,
+                                         C.c_void_p]
+    lib.uwie_vgg_enhance_bwd.restype = C.c_int
     lib.uwie_vgg_features_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
                                          C.c_void_p]
     lib.uwie_vgg_features_u8.restype = C.c_int
@@ -109,6 +124,32 @@ def load() -> C.CDLL:
     lib.uwie_quality_scores.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_void_p,
                                         C.c_void_p, C.c_size_t, C.c_void_p]
     lib.uwie_quality_scores.restype = C.c_int
+    vp, ci, cd, cf, cz = C.c_void_p, C.c_int, C.c_double, C.c_float, C.c_size_t
+    sigs = {
+        "uwie_prim_transmission_head_u8": ([vp, ci, ci, ci, vp, cf, cf, ci, vp, vp], ci),
+        "uwie_prim_clahe_lab_workspace_bytes": ([ci, ci, ci], cz),
+        "uwie_prim_clahe_lab": ([vp, ci, ci, ci, cd, ci, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_equalize_hist": ([vp, ci, ci, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_quantise": ([vp, ci, cz, vp, vp], ci),
+        "uwie_prim_atmospheric_light_workspace_bytes": ([ci, ci], cz),
+        "uwie_prim_atmospheric_light": ([vp, ci, ci, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_guided_filter_workspace_bytes": ([ci, ci], cz),
+        "uwie_prim_guided_filter": ([vp, vp, ci, ci, ci, cd, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_transmission_workspace_bytes": ([ci, ci], cz),
+        "uwie_prim_transmission": ([vp, ci, ci, ci, vp, cd, ci, cd, cd, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_recover": ([vp, ci, ci, ci, vp, vp, vp, ci, vp], ci),
+        "uwie_prim_percentile_stretch_workspace_bytes": ([ci], cz),
+        "uwie_prim_percentile_stretch": ([vp, ci, ci, ci, cd, cd, cd, vp, vp, cz, vp], ci),
+        "uwie_prim_gamma": ([vp, ci, cz, cd, ci, vp, vp], ci),
+        "uwie_prim_scale_clip": ([vp, ci, ci, ci, C.POINTER(C.c_double), vp, vp], ci),
+        "uwie_prim_channel_means": ([vp, ci, ci, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_region_score_workspace_bytes": ([ci, ci], cz),
+        "uwie_prim_region_score": ([vp, ci, ci, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_brightest_pixel": ([vp, ci, ci, ci, vp, vp, cz, vp], ci),
+    }
+    for name, (args, res) in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes, fn.restype = args, res
     lib.uwie_selftest_division.argtypes = [C.c_ulonglong, C.c_ulonglong, C.POINTER(C.c_ulonglong)]
     lib.uwie_selftest_division.restype = C.c_int
     _lib = lib

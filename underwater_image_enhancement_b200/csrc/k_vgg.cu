@@ -353,6 +353,84 @@ int grid_for(long long items) {
     return (int)g;
 }
 
+// ---------------------------------------------------------------- backward of the enhancement (training-time use)
+// d loss / d omega and d loss / d gamma of out = clamp(pow(clamp((s - .6) / clamp(1 - omega * min_c s, .1, 1) + .6, 0, 1) + 1e-8,
+// gamma), 0, 1) with s the stretched pixel: what autograd derives for vgg_16_UIE.py:32-128.  L_low / L_high receive no gradient
+// in the reference either (they pass through .item(), VGG:78-79).  torch.clamp passes the gradient on the closed interval.
+__global__ void __launch_bounds__(NT) vgg_enhance_bwd_kernel(const float* __restrict__ img, const float* __restrict__ gout, long long n,
+                                                             const SelState* __restrict__ state, const EnhanceParams* __restrict__ prm,
+                                                             double* __restrict__ gparams /* [2][batch] */, int batch) {
+    const int b = blockIdx.y;
+    __shared__ float lo[3], rng[3];
+    if (threadIdx.x < 3) {
+        const float p_lo = state[(b * 3 + threadIdx.x) * kTargets + 0].value;
+        const float p_hi = state[(b * 3 + threadIdx.x) * kTargets + 1].value;
+        lo[threadIdx.x] = p_lo;
+        rng[threadIdx.x] = __fadd_rn(__fsub_rn(p_hi, p_lo), 1e-8f);
+    }
+    __syncthreads();
+    const float omega = prm[b].omega, gamma = prm[b].gamma;
+    const float* p = img + (size_t)b * 3 * n;
+    const float* g = gout + (size_t)b * 3 * n;
+    double g_om = 0.0, g_ga = 0.0;
+    for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < n; i += (long long)gridDim.x * NT) {
+        float s[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) s[c] = clamp01(__fdiv_rn(__fsub_rn(p[c * n + i], lo[c]), rng[c]));
+        const float d = fminf(fminf(s[0], s[1]), s[2]);
+        const float traw = __fsub_rn(1.0f, __fmul_rn(omega, d));
+        const float t = fminf(fmaxf(traw, 0.1f), 1.0f);
+        float gt = 0.f;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float zraw = __fadd_rn(__fdiv_rn(__fsub_rn(s[c], 0.6f), t), 0.6f);
+            const float z = clamp01(zraw);
+            const float base = __fadd_rn(z, 1e-8f);
+            const float y = powf(base, gamma);
+            float gy = g[c * n + i];
+            if (!(y >= 0.f && y <= 1.f)) gy = 0.f;                       // final clamp
+            g_ga += (double)(gy * y * logf(base));
+            float gz = gy * gamma * powf(base, gamma - 1.0f);
+            if (!(zraw >= 0.f && zraw <= 1.f)) gz = 0.f;                  // clamp after the recovery
+            gt += gz * (-(s[c] - 0.6f) / (t * t));
+        }
+        if (traw >= 0.1f && traw <= 1.0f) g_om += (double)(gt * (-d));    // clamp of t
+    }
+    __shared__ double red[NT / 32][2];
+    g_om = warp_sum_f64(g_om); g_ga = warp_sum_f64(g_ga);
+    if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5][0] = g_om; red[threadIdx.x >> 5][1] = g_ga; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        double v = 0;
+        for (int w = 0; w < NT / 32; ++w) v += red[w][threadIdx.x];
+        atomicAdd(&gparams[threadIdx.x * batch + b], v);
+    }
+}
+
+// device-resident parameters (the network's outputs): ranks int(L / 100.0 * n) in double arithmetic (VGG:78-82),
+// clamped like use_trained_model.py:74-79 when `clamp_ranges` is set
+__global__ void vgg_params_kernel(const float* __restrict__ p /* [4][batch]: L_low, L_high, omega, gamma */, int batch,
+                                  long long n, int clamp_ranges, SelState* __restrict__ state, EnhanceParams* __restrict__ prm,
+                                  float* __restrict__ used /* [4][batch] or null: the values actually applied */) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= batch) return;
+    float llo = p[b], lhi = p[batch + b], om = p[2 * batch + b], ga = p[3 * batch + b];
+    if (clamp_ranges) {
+        llo = fminf(fmaxf(llo, 1.0f), 30.0f); lhi = fminf(fmaxf(lhi, 65.0f), 99.0f);
+        om = fminf(fmaxf(om, 0.1f), 0.9f); ga = fminf(fmaxf(ga, 0.5f), 3.0f);
+    }
+    long long lo = (long long)(((double)llo / 100.0) * (double)n);
+    long long hi = (long long)(((double)lhi / 100.0) * (double)n);
+    lo = lo < 0 ? 0 : (lo > n - 1 ? n - 1 : lo);
+    hi = hi < 0 ? 0 : (hi > n - 1 ? n - 1 : hi);
+    for (int c = 0; c < 3; ++c) {
+        state[(size_t)(b * 3 + c) * kTargets + 0] = SelState{lo, 0u, 0.f};
+        state[(size_t)(b * 3 + c) * kTargets + 1] = SelState{hi, 0u, 0.f};
+    }
+    prm[b].omega = om; prm[b].gamma = ga;
+    if (used) { used[b] = llo; used[batch + b] = lhi; used[2 * batch + b] = om; used[3 * batch + b] = ga; }
+}
+
 }  // namespace
 
 extern "C" {
@@ -400,6 +478,49 @@ int uwie_vgg_enhance(const float* img_dev, int batch, int height, int width, con
     vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
     vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist);
     vgg_enhance_kernel<<<dim3(grid_for(n / 4 + 1), batch), NT, 0, st>>>(img_dev, out_dev, n, state, prm, omega ? 1 : 0, gamma ? 1 : 0);
+    CUV(cudaGetLastError());
+    return UWIE_OK;
+}
+
+int uwie_vgg_enhance_dev(const float* img_dev, int batch, int height, int width, const float* params_dev, int clamp_ranges,
+                         float* used_dev, float* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream) {
+    if (!img_dev || !out_dev || !params_dev || batch < 1 || height < 1 || width < 1)
+        return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance_dev: bad arguments");
+    const VggLayout L = vgg_layout(batch);
+    if (!workspace_dev || workspace_bytes < L.total) return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance_dev: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)workspace_dev;
+    const long long n = (long long)height * width;
+    SelState* state = (SelState*)(ws + L.state);
+    EnhanceParams* prm = (EnhanceParams*)(ws + L.prm);
+    unsigned* hist = (unsigned*)(ws + L.hist);
+    vgg_params_kernel<<<(batch + 127) / 128, 128, 0, st>>>(params_dev, batch, n, clamp_ranges, state, prm, used_dev);
+    CUV(cudaMemsetAsync(hist, 0, (size_t)batch * 3 * kTargets * kBinsAB * 4, st));
+    const int planes = batch * 3;
+    const dim3 grid(grid_for(n / 4 + 1), planes);
+    vgg_sel_hist_kernel<0><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
+    vgg_sel_scan_kernel<0><<<planes, NT, 0, st>>>(state, hist);
+    vgg_sel_hist_kernel<1><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
+    vgg_sel_scan_kernel<1><<<planes, NT, 0, st>>>(state, hist);
+    vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
+    vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist);
+    vgg_enhance_kernel<<<dim3(grid_for(n / 4 + 1), batch), NT, 0, st>>>(img_dev, out_dev, n, state, prm, 1, 1);
+    CUV(cudaGetLastError());
+    return UWIE_OK;
+}
+
+int uwie_vgg_enhance_bwd(const float* img_dev, const float* grad_out_dev, int batch, int height, int width,
+                         const void* workspace_dev, size_t workspace_bytes, double* grad_params_dev, void* stream) {
+    if (!img_dev || !grad_out_dev || !grad_params_dev || batch < 1 || height < 1 || width < 1)
+        return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance_bwd: bad arguments");
+    const VggLayout L = vgg_layout(batch);
+    if (!workspace_dev || workspace_bytes < L.total) return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance_bwd: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const char* ws = (const char*)workspace_dev;
+    const long long n = (long long)height * width;
+    CUV(cudaMemsetAsync(grad_params_dev, 0, sizeof(double) * 2 * batch, st));
+    vgg_enhance_bwd_kernel<<<dim3(grid_for(n), batch), NT, 0, st>>>(img_dev, grad_out_dev, n, (const SelState*)(ws + L.state),
+                                                                  (const EnhanceParams*)(ws + L.prm), grad_params_dev, batch);
     CUV(cudaGetLastError());
     return UWIE_OK;
 }

@@ -575,6 +575,29 @@ int uwie_enhance_score(uwie_engine* e, const uint8_t* frames_dev, int batch, uin
                          light_dev, static_cast<cudaStream_t>(stream));
 }
 
+// detect_image_type (six_stadigy.py:292-302) of a batch: channel histograms + the colour-cast set-up kernel only.
+int uwie_engine_image_types(uwie_engine* e, const uint8_t* frames_dev, int batch, int32_t* type_dev, void* stream) {
+    if (!e || !frames_dev || !type_dev) return fail(UWIE_ERR_ARG, "null engine, frames or output");
+    if (batch < 1 || batch > e->B) return fail(UWIE_ERR_ARG, "batch must be in [1, max_batch]");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const Layout& L = e->L;
+    CU(cudaMemsetAsync(e->ws + L.frame_hist, 0, (size_t)batch * 768 * 4, st));
+    launch_frame_hist(frames_dev, batch, e->H, e->W, e->at<unsigned>(L.frame_hist), st);
+    SetupArgs sa;
+    sa.B = batch; sa.S = e->S; sa.n = (long long)e->H * e->W; sa.lib = e->lib;
+    sa.lib.colour_cast = 1;                                  // the type is wanted even by an engine that does not correct
+    sa.recipes = e->at<Recipe>(L.recipes);
+    sa.frame_hist = e->at<unsigned>(L.frame_hist);
+    sa.out_hist = e->at<unsigned>(L.out_hist);
+    sa.types = e->at<int>(L.types);
+    sa.cast = e->at<CastTables>(L.cast);
+    sa.tables = e->at<StratTables>(L.tables);
+    launch_setup_cast(sa, st);
+    CU(cudaMemcpyAsync(type_dev, sa.types, sizeof(int) * batch, cudaMemcpyDeviceToDevice, st));
+    CU(cudaGetLastError());
+    return UWIE_OK;
+}
+
 int uwie_engine_check(uwie_engine* e, void* stream) {
     if (!e) return fail(UWIE_ERR_ARG, "null engine");
     cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -102,6 +102,17 @@ class Engine:
         return {"out": out_all, "best_out": out_best, "scores": scores, "best": best, "type": types,
                 "light": light}
 
+    def image_types(self, frames: torch.Tensor) -> torch.Tensor:
+        """detect_image_type (six_stadigy.py:292-302) of uint8 CUDA frames [B, H, W, 3] -> int32 [B]
+        (0 normal / 1 greenish / 2 bluish); only the channel histograms and the colour-cast set-up run."""
+        frames = frames.contiguous()
+        B = frames.shape[0]
+        types = torch.empty((B,), dtype=torch.int32, device=frames.device)
+        stream = C.c_void_p(torch.cuda.current_stream(frames.device).cuda_stream)
+        with torch.cuda.device(frames.device):
+            _lib.check(self._lib.uwie_engine_image_types(self._h, _ptr(frames), B, _ptr(types), stream))
+        return types
+
     def check(self):
         """Synchronise and raise if the device reported a failure (e.g. selection overflow)."""
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)

@@ -37,12 +37,36 @@ def _floats(x, batch, name):
     return (C.c_float * batch)(*arr.tolist())
 
 
+def _needs_grad(img, params) -> bool:
+    if not torch.is_grad_enabled():
+        return False
+    ts = [img] + [v for v in params.values() if isinstance(v, torch.Tensor)]
+    return any(t.requires_grad for t in ts)
+
+
 class DifferentiableEnhancement:
-    """vgg_16_UIE.py:24-128, inference only: forward(img, params) on a CUDA float32 NCHW batch."""
+    """vgg_16_UIE.py:24-128: forward(img, params) on a CUDA float32 NCHW batch.
+
+    Inference (no gradient wanted) runs the fused selection + enhancement kernels.  When autograd is recording and the
+    image or a parameter requires grad (the training loops, vgg_16_UIE.py:529 / deep_learning_parameters.py:281), the
+    call goes through autograd_enhance.EnhanceFunction, whose backward is a CUDA kernel too; it never silently returns
+    a graph-less tensor."""
+
+    def to(self, *a, **k):            # nn.Module look-alikes used by use_trained_model.py:27
+        return self
+
+    def eval(self):
+        return self
+
+    def train(self, mode=True):
+        return self
 
     def forward(self, img: torch.Tensor, params: dict) -> torch.Tensor:
         if not (isinstance(img, torch.Tensor) and img.is_cuda):
             raise ValueError("img must be a CUDA tensor: the enhancement has no CPU path")
+        if _needs_grad(img, params):
+            from .autograd_enhance import enhance_with_grad
+            return enhance_with_grad(img, params)
         if img.dim() != 4 or img.shape[1] != 3:
             raise ValueError(f"img must be (B, 3, H, W), got {tuple(img.shape)}")
         img = img.contiguous().to(torch.float32)
@@ -61,6 +85,27 @@ class DifferentiableEnhancement:
         return out
 
     __call__ = forward
+
+    def forward_dev(self, img: torch.Tensor, params_dev: torch.Tensor, clamp_ranges: bool = False):
+        """Same enhancement with the parameters resident on the device: params_dev float32 [4, B] = rows L_low, L_high,
+        omega, gamma (uwie_vgg_enhance_dev).  Returns (enhanced, used [4, B]); nothing synchronises."""
+        if not (img.is_cuda and params_dev.is_cuda):
+            raise ValueError("img and params_dev must be CUDA tensors")
+        img = img.contiguous().to(torch.float32)
+        B, _, H, W = img.shape
+        params_dev = params_dev.to(torch.float32).contiguous()
+        if tuple(params_dev.shape) != (4, B):
+            raise ValueError(f"params_dev must be [4, {B}], got {tuple(params_dev.shape)}")
+        out = torch.empty_like(img)
+        used = torch.empty_like(params_dev)
+        ws, need = _workspace(B, img.device)
+        with torch.cuda.device(img.device):
+            _lib.check(_lib.load().uwie_vgg_enhance_dev(C.c_void_p(img.data_ptr()), B, H, W, C.c_void_p(params_dev.data_ptr()),
+                                                        int(bool(clamp_ranges)), C.c_void_p(used.data_ptr()),
+                                                        C.c_void_p(out.data_ptr()), C.c_void_p(ws.data_ptr()), need,
+                                                        _stream(img.device)))
+        ws.record_stream(torch.cuda.current_stream(img.device))
+        return out, used
 
 
 def _frames_u8(img, device):
