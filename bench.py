@@ -538,8 +538,12 @@ def measure_library(torch, dist, args, library, contract, dev, rank, world, host
     e2e_value = world * ne * args.steps / float(t.item())
     h2d = ne * NPIX * 3
     d2h = ne * (S if want_all else 1) * NPIX * 3 + ne * (S * 9 * 8 + 4 + 4 + 12)
-    # the host path must agree with the device path on the same frames
-    same = np.array_equal(res["scores"], scores[:ne].cpu().numpy())
+    # the host path must agree with the device path on the same frames: bytes and selection exactly; scores to 1e-9
+    # (the two paths use different chunk sizes, hence different row chunks in the float64 guided-filter sums: the
+    # float64 library's scores then differ in the last bits, the float32 library's not at all)
+    d_scores = scores[:ne].cpu().numpy()
+    score_diff = float(np.max(np.abs(res["scores"] - d_scores) / np.maximum(np.abs(d_scores), 1e-9)))
+    same = score_diff <= 1e-9 and np.array_equal(res["best"], best[:ne].cpu().numpy())
     if want_all:
         same = same and np.array_equal(h_out.numpy()[0], out_all[0].cpu().numpy())
     else:
@@ -592,7 +596,7 @@ def measure_library(torch, dist, args, library, contract, dev, rank, world, host
         "roofline": roofline, "gather_checked": gather_ok, "S": S, "chunk": chunk, "lanes": lanes,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "frames_per_step": ne, "chunk": e2e_chunk, "api": "uwie_enhance_score_host (C ABI, pinned host buffers)",
-                "matches_device_path": bool(same)},
+                "matches_device_path": bool(same), "max_score_rel_diff_vs_device_path": score_diff},
     }
 
 

@@ -209,7 +209,8 @@ int uwie_quality_scores(const void* img_dev, int dtype, int batch, int height, i
  *   colour 35 (FE:17-77) | texture 22 (FE:80-120) | frequency 5 (FE:123-158) | edge 7 (FE:161-200) |
  *   quality 10 (FE:203-246).
  * Stateless, asynchronous on `stream`; `workspace_dev` must hold uwie_features79_workspace_bytes(...).
- * The DCT of the frequency group runs as two float32 GEMMs through cuBLAS.
+ * The DCT of the frequency group is hand-written (csrc/k_dct.cu: float32 GEMMs with the even / odd butterfly, the
+ * coefficient plane reduced in the epilogue); its cosine matrices are built once per (device, length) and cached.
  * ------------------------------------------------------------------------------------------- */
 #define UWIE_FEATURES 79
 size_t uwie_features79_workspace_bytes(int batch, int height, int width);

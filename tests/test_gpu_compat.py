@@ -34,7 +34,10 @@ def test_apply_strategy_matches_reference(g):
         assert np.array_equal((out * 255).astype(np.uint8), g["p5_out"][i]), name
     with pytest.raises(ValueError):
         compat.es_apply_strategy(img, "white_balance", {})                      # ES:500-501
-    bad = np.random.default_rng(0).random((16, 16, 3))                          # not made from bytes: prints, returns input
+    rnd = np.random.default_rng(0).random((64, 64, 3))                          # not made from bytes: the primitive route
+    out = compat.es_apply_strategy(rnd, "clahe_enhancement", {})                # example_usage.py:27-31
+    assert out is not rnd and out.shape == rnd.shape and out.dtype == np.float64
+    bad = np.zeros((16, 16))                                                    # a failure inside: prints, returns input
     assert compat.es_apply_strategy(bad, "clahe_enhancement", {}) is bad        # ES:506-508
 
 

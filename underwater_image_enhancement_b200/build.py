@@ -21,7 +21,7 @@ LIB = os.path.join(PKG, "libuwie_b200.so")
 HOSTCHECK = os.path.join(ROOT, "tests", "_hostcheck.so")
 
 CU_SOURCES = ("k_stats.cu", "k_setup.cu", "k_canny.cu", "k_quadtree.cu", "k_guided.cu", "k_select.cu",
-              "k_apply.cu", "k_score.cu", "k_vgg.cu", "k_features.cu", "k_qa.cu", "k_prims.cu", "uwie_engine.cu")
+              "k_apply.cu", "k_score.cu", "k_vgg.cu", "k_features.cu", "k_qa.cu", "k_prims.cu", "k_dct.cu", "uwie_engine.cu")
 CPP_SOURCES = ("uwie_tables.cpp",)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -64,7 +64,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(_run, jobs))
     if force or jobs or not _newer(LIB, objs):
-        _run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart", "-lcublas"])
+        _run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"])
     hc_srcs = [os.path.join(CSRC, "hostcheck.cpp"), os.path.join(CSRC, "uwie_tables.cpp")]
     if force or not _newer(HOSTCHECK, hc_srcs + headers):
         _run(["g++", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-o", HOSTCHECK] + hc_srcs)

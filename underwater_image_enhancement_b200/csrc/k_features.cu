@@ -12,7 +12,6 @@
 //   GLCM               thumbnail (cv2.resize fixed point) -> 4 co-occurrence matrices by atomics -> properties
 //   DCT                D_H * G * D_W^T as two SGEMMs (cuBLAS, plain library GEMMs in full float32) + one reduction
 //   fe_final_kernel    everything that is a function of the histograms and sums, in float64
-#include <cublas_v2.h>
 #include <cuda_runtime.h>
 
 #include <cmath>
@@ -26,6 +25,7 @@
 #include "uwie_tables.h"
 
 namespace uwie {
+int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, double* sums, cudaStream_t st);
 int uwie_fail(int code, const std::string& msg);   // uwie_engine.cu
 }
 using namespace uwie;
@@ -303,41 +303,12 @@ __global__ void __launch_bounds__(NT) fe_glcm_props_kernel(const unsigned* __res
 }
 
 // ---------------------------------------------------------------- DCT
-// orthonormal DCT-II matrix, row-major [n][n]: D[k][i] = c_k cos(pi (2i + 1) k / (2n))
-__global__ void __launch_bounds__(NT) fe_dct_matrix_kernel(float* __restrict__ D, int n) {
-    const long long e = (long long)blockIdx.x * NT + threadIdx.x;
-    if (e >= (long long)n * n) return;
-    const int k = (int)(e / n), i = (int)(e - (long long)k * n);
-    // reduce the angle exactly in integers before the cosine: (2i + 1) k mod 4n
-    const long long q = ((2LL * i + 1) * k) % (4LL * n);
-    const double ck = k == 0 ? sqrt(1.0 / n) : sqrt(2.0 / n);
-    D[e] = (float)(ck * cospi((double)q / (2.0 * n)));
-}
-
-// sums over the coefficient plane: energy in the three blocks of FE:142-148, total energy, sum of |z|
-__global__ void __launch_bounds__(NT) fe_dct_reduce_kernel(const float* __restrict__ Z, int H, int W, FeAccum* __restrict__ acc) {
-    __shared__ double scratch[NT / 32];
-    const int b = blockIdx.y;
-    const float* z = Z + (size_t)b * H * W;
-    const long long n = (long long)H * W;
-    const int h4 = H / 4, h2 = H / 2, w4 = W / 4, w2 = W / 2;
-    double tot = 0, lo = 0, mid = 0, hi = 0, ab = 0;
-    for (long long e = (long long)blockIdx.x * NT + threadIdx.x; e < n; e += (long long)gridDim.x * NT) {
-        const int y = (int)(e / W), x = (int)(e - (long long)y * W);
-        const float v = z[e];
-        const double s = (double)__fmul_rn(v, v);                 // dct ** 2 is a float32 array
-        tot += s; ab += (double)fabsf(v);
-        if (y < h4 && x < w4) lo += s;
-        else if (y >= h4 && y < h2 && x >= w4 && x < w2) mid += s;
-        else if (y >= h2 && x >= w2) hi += s;
-    }
-    tot = block_sum(tot, scratch); lo = block_sum(lo, scratch); mid = block_sum(mid, scratch);
-    hi = block_sum(hi, scratch); ab = block_sum(ab, scratch);
-    if (threadIdx.x == 0) {
-        FeAccum& A = acc[b];
-        atomicAdd(&A.dct_total, tot); atomicAdd(&A.dct_low, lo); atomicAdd(&A.dct_mid, mid);
-        atomicAdd(&A.dct_high, hi); atomicAdd(&A.dct_abs, ab);
-    }
+__global__ void fe_copy_dct_kernel(const double* __restrict__ sums, FeAccum* __restrict__ acc, int B) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    FeAccum& A = acc[b];
+    A.dct_total = sums[b * 5]; A.dct_low = sums[b * 5 + 1]; A.dct_mid = sums[b * 5 + 2];
+    A.dct_high = sums[b * 5 + 3]; A.dct_abs = sums[b * 5 + 4];
 }
 
 // ---------------------------------------------------------------- final: 79 values per frame, float64
@@ -441,7 +412,7 @@ __global__ void fe_copy_canny_kernel(const unsigned* __restrict__ counts, FeAccu
     if (b < B) acc[b].canny = counts[b];
 }
 
-struct FeLayout { size_t ctab, acc, canny_counts, gray, grayf, tmp, coef, dh, dw, thumb, glcm, labels, tile_list, tile_n, total; };
+struct FeLayout { size_t ctab, acc, canny_counts, dct_sums, gray, grayf, tmp, thumb, glcm, labels, tile_list, tile_n, total; };
 FeLayout fe_layout(int B, int H, int W) {
     FeLayout L;
     size_t off = 0;
@@ -450,12 +421,10 @@ FeLayout fe_layout(int B, int H, int W) {
     L.ctab = take(sizeof(ColorTables));
     L.acc = take((size_t)B * sizeof(FeAccum));
     L.canny_counts = take((size_t)B * 4);
+    L.dct_sums = take((size_t)B * 5 * 8);
     L.gray = take(B * N);
     L.grayf = take(B * N * 4);
     L.tmp = take(B * N * 4);
-    L.coef = take(B * N * 4);
-    L.dh = take((size_t)H * H * 4);
-    L.dw = take((size_t)W * W * 4);
     L.thumb = take((size_t)B * kThumb * kThumb);
     L.glcm = take((size_t)B * 4 * 65536 * 4);
     L.labels = take(B * N * 4);
@@ -471,15 +440,6 @@ FeLayout fe_layout(int B, int H, int W) {
         cudaError_t _e = (call);                                                                   \
         if (_e != cudaSuccess) return uwie_fail(UWIE_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e)); \
     } while (0)
-#define CBL(call)                                                                                  \
-    do {                                                                                           \
-        cublasStatus_t _s = (call);                                                                \
-        if (_s != CUBLAS_STATUS_SUCCESS) return uwie_fail(UWIE_ERR_CUDA, std::string(#call) + ": cuBLAS status " + std::to_string((int)_s)); \
-    } while (0)
-
-std::mutex g_blas_mu;
-cublasHandle_t g_blas[64] = {};          // one handle per device ordinal
-
 const ColorTables& host_tables() {
     static ColorTables t;
     static std::once_flag once;
@@ -513,15 +473,14 @@ int uwie_features79(const uint8_t* frames_dev, int batch, int height, int width,
     uint8_t* gray = (uint8_t*)(ws + L.gray);
     float* grayf = (float*)(ws + L.grayf);
     float* tmp = (float*)(ws + L.tmp);
-    float* coef = (float*)(ws + L.coef);
-    float* dh = (float*)(ws + L.dh);
-    float* dw = (float*)(ws + L.dw);
+    double* dct_sums = (double*)(ws + L.dct_sums);
     uint8_t* thumb = (uint8_t*)(ws + L.thumb);
     unsigned* glcm = (unsigned*)(ws + L.glcm);
 
     CUF(cudaMemcpyAsync(ctab, &host_tables(), sizeof(ColorTables), cudaMemcpyHostToDevice, st));
     CUF(cudaMemsetAsync(acc, 0, (size_t)B * sizeof(FeAccum), st));
     CUF(cudaMemsetAsync(canny_counts, 0, (size_t)B * 4, st));
+    CUF(cudaMemsetAsync(dct_sums, 0, (size_t)B * 5 * 8, st));
     CUF(cudaMemsetAsync(glcm, 0, (size_t)B * 4 * 65536 * 4, st));
 
     int pb = (int)((N + NT * 8 - 1) / (NT * 8));
@@ -549,27 +508,11 @@ int uwie_features79(const uint8_t* frames_dev, int batch, int height, int width,
     fe_glcm_count_kernel<<<dim3(kThumb * kThumb / NT, B), NT, 0, st>>>(thumb, glcm);
     fe_glcm_props_kernel<<<dim3(4, B), NT, 0, st>>>(glcm, acc);
 
-    // DCT: coef = D_H * G * D_W^T.  Row-major buffers are column-major transposes, so in cuBLAS terms
-    //   tmp^T (W x H)  = G^T (W x H)  * D_H^T (H x H)          = gemm(N, N) on (grayf, dh)
-    //   coef^T (W x H) = D_W (W x W)  * tmp^T (W x H)          = gemm(T, N) on (dw, tmp)
-    fe_dct_matrix_kernel<<<(int)(((long long)H * H + NT - 1) / NT), NT, 0, st>>>(dh, H);
-    fe_dct_matrix_kernel<<<(int)(((long long)W * W + NT - 1) / NT), NT, 0, st>>>(dw, W);
-    {
-        int dev = 0;
-        CUF(cudaGetDevice(&dev));
-        std::lock_guard<std::mutex> lock(g_blas_mu);
-        if (dev < 0 || dev >= 64) return uwie_fail(UWIE_ERR_ARG, "uwie_features79: device ordinal out of range");
-        if (!g_blas[dev]) {
-            CBL(cublasCreate(&g_blas[dev]));
-            CBL(cublasSetMathMode(g_blas[dev], CUBLAS_PEDANTIC_MATH));      // plain float32, no TF32
-        }
-        cublasHandle_t hb = g_blas[dev];
-        CBL(cublasSetStream(hb, st));
-        const float one = 1.f, zero = 0.f;
-        CBL(cublasSgemmStridedBatched(hb, CUBLAS_OP_N, CUBLAS_OP_N, W, H, H, &one, grayf, W, N, dh, H, 0, &zero, tmp, W, N, B));
-        CBL(cublasSgemmStridedBatched(hb, CUBLAS_OP_T, CUBLAS_OP_N, W, H, W, &one, dw, W, 0, tmp, W, N, &zero, coef, W, N, B));
-    }
-    fe_dct_reduce_kernel<<<dim3(pb, B), NT, 0, st>>>(coef, H, W, acc);
+    // DCT (k_dct.cu): D_H * G * D_W^T as hand-written float32 GEMMs with the even / odd butterfly; the coefficient plane is
+    // never stored, its five sums land in dct_sums
+    if (launch_dct_energy(grayf, tmp, B, H, W, dct_sums, st) < 0)
+        return uwie_fail(UWIE_ERR_NOMEM, "uwie_features79: the cached DCT matrices could not be allocated");
+    fe_copy_dct_kernel<<<(B + 127) / 128, 128, 0, st>>>(dct_sums, acc, B);
 
     const PercentilePlan q25 = percentile_plan_f32(N, 25.0), q75 = percentile_plan_f32(N, 75.0);
     RankPlan r25, r75;
