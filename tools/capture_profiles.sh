@@ -27,5 +27,12 @@ timeout 900 ncu --set full --clock-control none --import-source on --kernel-name
 timeout 300 python tools/prims_driver.py 2 > gpurun_out/${TAG}_plain_prims.log 2>&1 && \
 timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base demangled \
     -k regex:"thead_kernel|clahe_l_" -s 2 -c 3 -o gpurun_out/${TAG}_full_prims python tools/prims_driver.py 2 > gpurun_out/${TAG}_full_prims.log 2>&1
+# gpurun brings back at most 64 MiB: keep the raw-page CSVs (every metric of every captured launch) and drop the big reports
+for X in six es; do
+  if [ -f gpurun_out/${TAG}_full_${X}.ncu-rep ]; then
+    ncu -i gpurun_out/${TAG}_full_${X}.ncu-rep --page raw --csv > gpurun_out/${TAG}_full_${X}_raw.csv 2>/dev/null
+    rm -f gpurun_out/${TAG}_full_${X}.ncu-rep
+  fi
+done
 tail -c 400 gpurun_out/${TAG}_bench.json 2>/dev/null
 ls -la gpurun_out | tail -20
