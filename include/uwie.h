@@ -130,6 +130,11 @@ int uwie_engine_check(uwie_engine* e, void* stream);
 /* Kernels launched by the last uwie_enhance_score call on this engine. */
 int uwie_engine_last_launches(const uwie_engine* e);
 
+/* uwie_enhance_score[_host] replays its kernel sequence as ONE CUDA graph launch once it has seen the same batch size and
+ * buffer pointers twice on a capturable stream (not the legacy / per-thread default stream; UWIE_NO_GRAPH=1 disables it).
+ * Number of calls served by a graph replay so far (a diagnostic; the kernels and their results are the same). */
+long long uwie_engine_graph_replays(const uwie_engine* e);
+
 /* Per-stage device timing.  uwie_engine_profile(e, 1) clears the record and makes every following
  * uwie_enhance_score[_host] call bracket each stage of its kernel sequence with CUDA events on the
  * call's stream; (e, 0) stops.  uwie_engine_profile_read synchronises those events and returns, per
@@ -170,6 +175,12 @@ int uwie_vgg_enhance(const float* img_dev, int batch, int height, int width,
  * used_dev (may be NULL): float32 [4][batch], the values actually applied. */
 int uwie_vgg_enhance_dev(const float* img_dev, int batch, int height, int width, const float* params_dev, int clamp_ranges,
                          float* used_dev, float* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* The same with the frames still uint8 [batch][H][W][3] (imread bytes; use_trained_model.py:119 divides them by 255): the
+ * order statistics come from the channel histograms, so the frame is read twice as bytes instead of four times as floats.
+ * out_dev: float32 [batch][3][H][W].  Bit-identical to uwie_vgg_enhance_dev on frame / 255. */
+int uwie_vgg_enhance_u8(const uint8_t* frames_dev, int batch, int height, int width, const float* params_dev, int clamp_ranges,
+                        float* used_dev, float* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream);
 
 /* Backward of the enhancement for the training loops (vgg_16_UIE.py:529, deep_learning_parameters.py:281): given
  * d loss / d out (float32 NCHW), the input image and the WORKSPACE of the forward uwie_vgg_enhance[_dev] call on the same

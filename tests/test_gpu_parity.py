@@ -255,3 +255,35 @@ def test_bad_arguments_raise(cuda_device):
     with pytest.raises(_lib.UwieError):
         eng.run(torch.zeros((2, 64, 64, 3), dtype=torch.uint8, device="cuda"))
     eng.close()
+
+
+def test_graph_replay_is_the_same_computation(cuda_device):
+    """The third call with the same buffers on a capturable stream replays a CUDA graph of the kernel sequence
+    (uwie_engine_graph_replays): identical results, and new frame CONTENT in the same buffers is honoured."""
+    h, w = 96, 128
+    frames = np.stack([synth_image(s, h, w) for s in (0, 1)])
+    other = np.stack([synth_image(s, h, w) for s in (5, 6)])
+    eager = _run("six", frames)
+    eager_other = _run("six", other)
+    eng = Engine("six", h, w, max_batch=2)
+    d = torch.from_numpy(frames).cuda()
+    out = torch.empty((2, 6, h, w, 3), dtype=torch.uint8, device="cuda")
+    scores = torch.empty((2, 6, 9), dtype=torch.float64, device="cuda")
+    best = torch.empty((2,), dtype=torch.int32, device="cuda")
+    types = torch.empty((2,), dtype=torch.int32, device="cuda")
+    light = torch.empty((2, 3), dtype=torch.float32, device="cuda")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(4):
+            if i == 3:
+                d.copy_(torch.from_numpy(other).cuda())
+            eng.run(d, want_all=True, out_all=out, scores=scores, best=best, types=types, light=light)
+            eng.check()
+            want = eager if i < 3 else eager_other
+            assert np.array_equal(out.cpu().numpy(), want["out"]), i
+            assert np.array_equal(scores.cpu().numpy(), want["scores"]), i
+            assert np.array_equal(best.cpu().numpy(), want["best"]) and np.array_equal(light.cpu().numpy(), want["light"]), i
+    side.synchronize()
+    assert eng.graph_replays >= 2 and eng.last_launches > 0
+    eng.close()

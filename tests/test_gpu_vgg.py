@@ -99,3 +99,22 @@ def test_vgg_bad_arguments():
         enh(img.cpu(), {"L_low": [1.0], "L_high": [99.0]})
     with pytest.raises(ValueError):
         enh(img, {"L_low": [1.0, 2.0], "L_high": [99.0]})
+
+
+def test_enhance_from_bytes_equals_enhance_of_float_image(cuda_device):
+    """uwie_vgg_enhance_u8 (order statistics from the byte histograms, frame read as bytes) against uwie_vgg_enhance_dev on
+    frame / 255 and against the oracle: bit-identical / pow tolerance; the device-side clamps are use_trained_model.py:74-79."""
+    import torch
+    from underwater_image_enhancement_b200 import vgg
+    frames = np.stack([synth_image(90 + i, 135, 241) for i in range(3)])
+    d = torch.from_numpy(frames).cuda()
+    params = torch.tensor([[0.5, 12.0, 40.0], [99.5, 90.0, 60.0], [0.05, 0.6, 0.95], [0.4, 1.2, 3.5]], device="cuda")
+    out8, used8 = vgg.enhance_frames_u8(d, params, clamp_ranges=True)
+    img = (d.permute(0, 3, 1, 2).float() / 255.0).contiguous()
+    outf, usedf = vgg.DifferentiableEnhancement().forward_dev(img, params, clamp_ranges=True)
+    assert torch.equal(used8, usedf)
+    assert torch.equal(used8.cpu(), torch.tensor([[1.0, 12.0, 30.0], [99.0, 90.0, 65.0], [0.1, 0.6, 0.9], [0.5, 1.2, 3.0]]))
+    assert torch.equal(out8, outf)
+    u = used8.cpu().numpy()
+    want = o.vgg_enhance(img.cpu().numpy(), u[0], u[1], u[2], u[3])
+    assert np.abs(out8.cpu().numpy() - want).max() <= 1e-6

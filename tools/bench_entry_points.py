@@ -158,6 +158,10 @@ def main(cpu=None, out_path=None):
     cpu_s = cpu_time(cpu, "vgg_enhance", img[:1].cpu().numpy(), params["L_low"][:1], params["L_high"][:1],
                      params["omega"][:1], params["gamma"][:1])
     emit("vgg_enhance", "vgg_16_UIE.py:32-128", h, w, batch, 24, ms, "f32", cpu_s, "f32 NCHW in and out")
+    pdev = torch.tensor([params["L_low"], params["L_high"], params["omega"], params["gamma"]], dtype=torch.float32, device="cuda")
+    ms = time_ms(lambda: vgg.enhance_frames_u8(frames, pdev, True))
+    emit("vgg_enhance_u8", "vgg_16_UIE.py:32-128 on imread bytes (use_trained_model.py:119)", h, w, batch, 15, ms, "u8->f32", None,
+         "u8 HWC in, f32 NCHW out (15 N): order statistics from the byte histograms, frame read twice as bytes")
     ms = time_ms(lambda: vgg.extract_all_features(frames))
     cpu_s = cpu_time(cpu, "vgg_features", fr_np[0])
     emit("vgg_features", "vgg_16_UIE.py:435-466", h, w, batch, 3, ms, "u8->f32", cpu_s)

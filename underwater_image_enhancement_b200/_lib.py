@@ -17,8 +17,8 @@ OK, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_SELECT = 0, -1, -2, -3, -4
 EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_bytes", "uwie_engine_create",
            "uwie_engine_destroy", "uwie_enhance_score", "uwie_engine_host_prepare", "uwie_enhance_score_host",
            "uwie_engine_image_types", "uwie_engine_check",
-           "uwie_engine_last_launches", "uwie_engine_debug", "uwie_engine_profile",
-           "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_enhance_dev", "uwie_vgg_enhance_bwd", "uwie_vgg_features_u8",
+           "uwie_engine_last_launches", "uwie_engine_graph_replays", "uwie_engine_debug", "uwie_engine_profile",
+           "uwie_engine_profile_read", "uwie_vgg_workspace_bytes", "uwie_vgg_enhance", "uwie_vgg_enhance_dev", "uwie_vgg_enhance_u8", "uwie_vgg_enhance_bwd", "uwie_vgg_features_u8",
            "uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32", "uwie_features79_workspace_bytes",
            "uwie_features79", "uwie_quality_workspace_bytes", "uwie_quality_scores", "uwie_selftest_division",
            "uwie_prim_transmission_head_u8", "uwie_prim_clahe_lab_workspace_bytes", "uwie_prim_clahe_lab",
@@ -89,6 +89,8 @@ def load() -> C.CDLL:
     lib.uwie_engine_check.restype = C.c_int
     lib.uwie_engine_last_launches.argtypes = [C.c_void_p]
     lib.uwie_engine_last_launches.restype = C.c_int
+    lib.uwie_engine_graph_replays.argtypes = [C.c_void_p]
+    lib.uwie_engine_graph_replays.restype = C.c_longlong
     lib.uwie_engine_debug.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_size_t)]
     lib.uwie_engine_debug.restype = C.c_void_p
     lib.uwie_engine_profile.argtypes = [C.c_void_p, C.c_int]
@@ -105,6 +107,8 @@ def load() -> C.CDLL:
     lib.uwie_vgg_enhance_dev.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_size_t, C.c_void_p]
     lib.uwie_vgg_enhance_dev.restype = C.c_int
+    lib.uwie_vgg_enhance_u8.argtypes = lib.uwie_vgg_enhance_dev.argtypes
+    lib.uwie_vgg_enhance_u8.restype = C.c_int
     lib.uwie_vgg_enhance_bwd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p,
                                          C.c_void_p]
     lib.uwie_vgg_enhance_bwd.restype = C.c_int

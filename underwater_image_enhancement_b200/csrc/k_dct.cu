@@ -52,8 +52,12 @@ struct DctArgs {
 };
 
 // C[M x N] = A[M x K] * B[K x N], 128 x 128 tile per block, 8 x 8 per thread, operands through functors.
-template <class LoadA, class LoadB, class Epilogue>
-__device__ __forceinline__ void gemm_tile(int M, int N, int K, int m0, int n0, LoadA load_a, LoadB load_b, Epilogue epi) {
+// load_a4(m, k) / load_b4(k, n) return 4 consecutive k / n as one float4 (128-bit loads; the mirrored operand is one
+// reversed float4) and are used wherever the four elements are in range and `vec` says the rows are 16-byte aligned;
+// the scalar functors cover the ragged edges.
+template <class LoadA, class LoadB, class LoadA4, class LoadB4, class Epilogue>
+__device__ __forceinline__ void gemm_tile(int M, int N, int K, int m0, int n0, bool vec, LoadA load_a, LoadB load_b,
+                                          LoadA4 load_a4, LoadB4 load_b4, Epilogue epi) {
     __shared__ __align__(16) float sA[2][BK][BM + 4];
     __shared__ __align__(16) float sB[2][BK][BN + 4];
     const int t = threadIdx.x;
@@ -67,17 +71,27 @@ __device__ __forceinline__ void gemm_tile(int M, int N, int K, int m0, int n0, L
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
     float ra[4], rb[4];
     auto fetch = [&](int k0) {
+        const int m = m0 + a_row, ka = k0 + a_k;
+        if (vec && m < M && ka + 3 < K) {
+            const float4 v = load_a4(m, ka);
+            ra[0] = v.x; ra[1] = v.y; ra[2] = v.z; ra[3] = v.w;
+        } else {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int m = m0 + a_row, k = k0 + a_k + j;
-            ra[j] = (m < M && k < K) ? load_a(m, k) : 0.f;
-            const int kk = k0 + b_k, n = n0 + b_n + j;
-            rb[j] = (kk < K && n < N) ? load_b(kk, n) : 0.f;
+            for (int j = 0; j < 4; ++j) ra[j] = (m < M && ka + j < K) ? load_a(m, ka + j) : 0.f;
+        }
+        const int kb = k0 + b_k, n = n0 + b_n;
+        if (vec && kb < K && n + 3 < N) {
+            const float4 v = load_b4(kb, n);
+            rb[0] = v.x; rb[1] = v.y; rb[2] = v.z; rb[3] = v.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) rb[j] = (kb < K && n + j < N) ? load_b(kb, n + j) : 0.f;
         }
     };
     auto stash = [&](int buf) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { sA[buf][a_k + j][a_row] = ra[j]; sB[buf][b_k][b_n + j] = rb[j]; }
+        for (int j = 0; j < 4; ++j) sA[buf][a_k + j][a_row] = ra[j];
+        *reinterpret_cast<float4*>(&sB[buf][b_k][b_n]) = make_float4(rb[0], rb[1], rb[2], rb[3]);
     };
     fetch(0);
     stash(0);
@@ -115,8 +129,13 @@ __device__ __forceinline__ void gemm_tile(int M, int N, int K, int m0, int n0, L
         }
 }
 
+__device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 add4(float4 u, float4 v, float s) {
+    return make_float4(__fadd_rn(u.x, s * v.x), __fadd_rn(u.y, s * v.y), __fadd_rn(u.z, s * v.z), __fadd_rn(u.w, s * v.w));
+}
+
 // step 1: T = D_H * G.  grid (ceil(W / 128), split_h * ceil(rows_p / 128), B); a row tile holds rows of ONE parity
-__global__ void __launch_bounds__(GNT) dct_rows_kernel(DctArgs a) {
+__global__ void __launch_bounds__(GNT, 2) dct_rows_kernel(DctArgs a) {
     const int b = blockIdx.z;
     const int H = a.H, W = a.W, sp = a.split_h;
     const int half = H / sp;                            // inner length
@@ -127,17 +146,23 @@ __global__ void __launch_bounds__(GNT) dct_rows_kernel(DctArgs a) {
     float* T = a.T + (size_t)b * H * W;
     const float* A = a.Ah + (size_t)p * half * half;
     const float sign = p ? -1.f : 1.f;
-    gemm_tile(half, W, half, m0, blockIdx.x * BN,
+    const bool vec = (half & 3) == 0 && (W & 3) == 0 && ((reinterpret_cast<uintptr_t>(G) | reinterpret_cast<uintptr_t>(A)) & 15) == 0;
+    gemm_tile(half, W, half, m0, blockIdx.x * BN, vec,
               [&](int m, int k) { return __ldg(&A[(size_t)m * half + k]); },
               [&](int k, int n) {
                   const float u = __ldg(&G[(size_t)k * W + n]);
                   return sp == 1 ? u : __fadd_rn(u, sign * __ldg(&G[(size_t)(H - 1 - k) * W + n]));
               },
+              [&](int m, int k) { return ld4(&A[(size_t)m * half + k]); },
+              [&](int k, int n) {
+                  const float4 u = ld4(&G[(size_t)k * W + n]);
+                  return sp == 1 ? u : add4(u, ld4(&G[(size_t)(H - 1 - k) * W + n]), sign);
+              },
               [&](int m, int n, float v) { T[(size_t)(sp * m + p) * W + n] = v; });
 }
 
 // step 2: Z = T * D_W^T, reduced in the epilogue.  grid (split_w * ceil(cols_p / 128), ceil(H / 128), B)
-__global__ void __launch_bounds__(GNT) dct_cols_kernel(DctArgs a) {
+__global__ void __launch_bounds__(GNT, 2) dct_cols_kernel(DctArgs a) {
     const int b = blockIdx.z;
     const int H = a.H, W = a.W, sp = a.split_w;
     const int half = W / sp;
@@ -149,12 +174,20 @@ __global__ void __launch_bounds__(GNT) dct_cols_kernel(DctArgs a) {
     const float sign = p ? -1.f : 1.f;
     const int h4 = H / 4, h2 = H / 2, w4 = W / 4, w2 = W / 2;
     double tot = 0, lo = 0, mid = 0, hi = 0, ab = 0;
-    gemm_tile(H, half, half, blockIdx.y * BM, n0,
+    const bool vec = (half & 3) == 0 && (W & 3) == 0 && ((reinterpret_cast<uintptr_t>(T) | reinterpret_cast<uintptr_t>(Bt)) & 15) == 0;
+    gemm_tile(H, half, half, blockIdx.y * BM, n0, vec,
               [&](int m, int k) {
                   const float u = __ldg(&T[(size_t)m * W + k]);
                   return sp == 1 ? u : __fadd_rn(u, sign * __ldg(&T[(size_t)m * W + (W - 1 - k)]));
               },
               [&](int k, int n) { return __ldg(&Bt[(size_t)k * half + n]); },
+              [&](int m, int k) {
+                  const float4 u = ld4(&T[(size_t)m * W + k]);
+                  if (sp == 1) return u;
+                  const float4 r = ld4(&T[(size_t)m * W + (W - 4 - k)]);      // elements W-1-k-3 .. W-1-k, reversed below
+                  return add4(u, make_float4(r.w, r.z, r.y, r.x), sign);
+              },
+              [&](int k, int n) { return ld4(&Bt[(size_t)k * half + n]); },
               [&](int y, int n, float v) {
                   const int x = sp * n + p;
                   const double s = (double)__fmul_rn(v, v);          // dct ** 2 is a float32 array (FE:142)

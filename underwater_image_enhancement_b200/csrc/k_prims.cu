@@ -209,19 +209,39 @@ __global__ void __launch_bounds__(CH_NT) clahe_l_hist_kernel(ClaheLArgs a) {
         unsigned* p = mine + (v >> 1) * CH_NT;
         *p += 1u << ((v & 1u) << 4);
     };
+    // two pixels at a time: both counter words are fetched before either is written back, so two shared-memory
+    // round trips overlap; a pair that hits the same word is merged (neighbouring pixels often do)
+    auto count2 = [&](unsigned v0, unsigned v1) {
+        unsigned* p0 = mine + (v0 >> 1) * CH_NT;
+        unsigned* p1 = mine + (v1 >> 1) * CH_NT;
+        const unsigned w0 = *p0, w1 = *p1;
+        const unsigned i0 = 1u << ((v0 & 1u) << 4), i1 = 1u << ((v1 & 1u) << 4);
+        const bool same = p0 == p1;
+        *p0 = w0 + i0 + (same ? i1 : 0u);
+        if (!same) *p1 = w1 + i1;
+    };
+    auto count_word = [&](unsigned w) {
+        count2(w & 255u, (w >> 8) & 255u);
+        count2((w >> 16) & 255u, w >> 24);
+    };
     const bool fast = x0 + a.tw <= a.W && y1 <= a.H && (a.tw & 15) == 0 && (a.W & 15) == 0 &&
                       (reinterpret_cast<uintptr_t>(img) & 15) == 0;
     if (fast) {
         const int vpr = a.tw >> 4;                          // 16-pixel vectors per tile row
         const int nvec = vpr * (y1 - y0);
-        for (int i = t; i < nvec; i += CH_NT) {
+        auto load = [&](int i) {
             const int ly = i / vpr, vx = i - ly * vpr;
-            const uint4 q = __ldg(reinterpret_cast<const uint4*>(img + (size_t)(y0 + ly) * a.W + x0) + vx);
-            const unsigned ws[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                count(ws[k] & 255u); count((ws[k] >> 8) & 255u); count((ws[k] >> 16) & 255u); count(ws[k] >> 24);
-            }
+            return __ldg(reinterpret_cast<const uint4*>(img + (size_t)(y0 + ly) * a.W + x0) + vx);
+        };
+        // the vectors of the next two rounds are in flight while this round's 16 pixels are counted
+        uint4 n0 = make_uint4(0, 0, 0, 0), n1 = n0;
+        if (t < nvec) n0 = load(t);
+        if (t + CH_NT < nvec) n1 = load(t + CH_NT);
+        for (int i = t; i < nvec; i += CH_NT) {
+            const uint4 q = n0;
+            n0 = n1;
+            if (i + 2 * CH_NT < nvec) n1 = load(i + 2 * CH_NT);
+            count_word(q.x); count_word(q.y); count_word(q.z); count_word(q.w);
         }
     } else {
         const int n = a.tw * max(y1 - y0, 0);
@@ -266,8 +286,7 @@ constexpr int CA_ROWS = 64;              // rows of a cell one block takes
 
 __global__ void __launch_bounds__(CA_NT) clahe_l_apply_kernel(ClaheLArgs a) {
     __shared__ float4 tab[256];
-    __shared__ float s_ya[CA_ROWS], s_ya1[CA_ROWS];
-    __shared__ int s_rowok[CA_ROWS];
+    __shared__ float2 s_yw[CA_ROWS];        // (ya, ya1) of a row; ya < 0 marks a row whose own floor() lands in another cell
     const int cells_x = a.tiles_x + 1;
     const int cyi = blockIdx.x / cells_x, cxi = blockIdx.x - cyi * cells_x;
     const int b = blockIdx.z, t = threadIdx.x;
@@ -291,7 +310,7 @@ __global__ void __launch_bounds__(CA_NT) clahe_l_apply_kernel(ClaheLArgs a) {
             const float tyf = __fsub_rn(__fmul_rn((float)(ys + r), inv_th), 0.5f);
             const float fl = floorf(tyf);
             const float ya = __fsub_rn(tyf, fl);
-            s_ya[r] = ya; s_ya1[r] = __fsub_rn(1.0f, ya); s_rowok[r] = ((int)fl == ty1);
+            s_yw[r] = ((int)fl == ty1) ? make_float2(ya, __fsub_rn(1.0f, ya)) : make_float2(-1.f, 0.f);
         }
     }
     __syncthreads();
@@ -310,6 +329,14 @@ __global__ void __launch_bounds__(CA_NT) clahe_l_apply_kernel(ClaheLArgs a) {
         const float bot = __fadd_rn(__fmul_rn((float)luts[(q2 * a.tiles_x + p1) * 256 + v], xa1), __fmul_rn((float)luts[(q2 * a.tiles_x + p2) * 256 + v], xa));
         return clampi(__float2int_rn(__fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya))), 0, 255);
     };
+    // a blend of values in [0, 255] with weights xa1 + xa = 1 (to an ulp) cannot leave [0, 255.0001]: cv2's saturate_cast
+    // is a plain round here, and so is this
+    auto blend = [&](int v, float xa, float xa1, float ya, float ya1) -> unsigned {
+        const float4 q = tab[v];
+        const float top = __fadd_rn(__fmul_rn(q.x, xa1), __fmul_rn(q.y, xa));
+        const float bot = __fadd_rn(__fmul_rn(q.z, xa1), __fmul_rn(q.w, xa));
+        return (unsigned)__float2int_rn(__fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya)));
+    };
     const bool words = (cx0 & 3) == 0 && (a.W & 3) == 0 && ((reinterpret_cast<uintptr_t>(img) | reinterpret_cast<uintptr_t>(out)) & 3) == 0;
     if (words) {
         const int gpr = (cx1 - cx0 + 3) >> 2;               // 4-pixel groups per row (the last may overhang the cell)
@@ -326,30 +353,30 @@ __global__ void __launch_bounds__(CA_NT) clahe_l_apply_kernel(ClaheLArgs a) {
                 okx[j] = ((int)fl == tx1);
             }
             const bool overhang = xg + 3 >= cx1;            // the last pixels of the word belong to the next cell
-            for (int r = r0; r < ye - ys; r += rstep) {
-                const int y = ys + r;
-                const size_t p = (size_t)y * a.W + xg;
-                const uint32_t wv = __ldg(reinterpret_cast<const uint32_t*>(img + p));
-                const float ya = s_ya[r], ya1 = s_ya1[r];
-                const bool oky = s_rowok[r] != 0;
-                uint32_t ov = 0;
+            const bool clean = okx[0] && okx[1] && okx[2] && okx[3] && !overhang;
+            const int nrows = ye - ys;
+            const uint8_t* src = img + (size_t)ys * a.W + xg;
+            uint8_t* dst = out + (size_t)ys * a.W + xg;
+            uint32_t nxt = r0 < nrows ? __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)r0 * a.W)) : 0u;
+            for (int r = r0; r < nrows; r += rstep) {
+                const uint32_t wv = nxt;
+                if (r + rstep < nrows) nxt = __ldg(reinterpret_cast<const uint32_t*>(src + (size_t)(r + rstep) * a.W));
+                const float2 yw = s_yw[r];
+                if (clean && yw.x >= 0.f) {
+                    const unsigned o0 = blend(wv & 255u, xa[0], xa1[0], yw.x, yw.y);
+                    const unsigned o1 = blend((wv >> 8) & 255u, xa[1], xa1[1], yw.x, yw.y);
+                    const unsigned o2 = blend((wv >> 16) & 255u, xa[2], xa1[2], yw.x, yw.y);
+                    const unsigned o3 = blend(wv >> 24, xa[3], xa1[3], yw.x, yw.y);
+                    *reinterpret_cast<uint32_t*>(dst + (size_t)r * a.W) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
+                } else {
+                    const int y = ys + r;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int v = (wv >> (8 * j)) & 255;
-                    int res = 0;
-                    if (okx[j] && oky) {
-                        const float4 q = tab[v];
-                        const float top = __fadd_rn(__fmul_rn(q.x, xa1[j]), __fmul_rn(q.y, xa[j]));
-                        const float bot = __fadd_rn(__fmul_rn(q.z, xa1[j]), __fmul_rn(q.w, xa[j]));
-                        res = clampi(__float2int_rn(__fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya))), 0, 255);
-                    } else if (xg + j < cx1) {
-                        res = slow(xg + j, y, v);
+                    for (int j = 0; j < 4; ++j) {
+                        if (xg + j >= cx1) continue;
+                        const int v = (wv >> (8 * j)) & 255;
+                        const unsigned res = (okx[j] && yw.x >= 0.f) ? blend(v, xa[j], xa1[j], yw.x, yw.y) : (unsigned)slow(xg + j, y, v);
+                        dst[(size_t)r * a.W + j] = (uint8_t)res;
                     }
-                    ov |= (uint32_t)res << (8 * j);
-                }
-                if (!overhang) *reinterpret_cast<uint32_t*>(out + p) = ov;
-                else {
-                    for (int j = 0; j < 4; ++j) if (xg + j < cx1) out[p + j] = (uint8_t)(ov >> (8 * j));
                 }
             }
         };

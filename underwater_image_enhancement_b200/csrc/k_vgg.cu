@@ -407,6 +407,65 @@ __global__ void __launch_bounds__(NT) vgg_enhance_bwd_kernel(const float* __rest
     }
 }
 
+// ---------------------------------------------------------------- the same enhancement straight from the uint8 frames
+// use_trained_model.py feeds imread / 255 (UTM:119): the float image takes 256 values per channel, so the order statistics
+// sorted[int(L / 100 * n)] follow from the channel histograms and the frame is read twice as BYTES (histogram, apply)
+// instead of four times as floats: 3 N + 3 N bytes in, 12 N out.
+__global__ void vgg_ranks_u8_kernel(const unsigned* __restrict__ hist /* [B][3][256] */, int batch, SelState* __restrict__ state) {
+    const int pc = blockIdx.x * blockDim.x + threadIdx.x;          // plane = b * 3 + c
+    if (pc >= batch * 3) return;
+    const unsigned* h = hist + (size_t)pc * 256;
+    for (int tg = 0; tg < kTargets; ++tg) {
+        SelState& st = state[(size_t)pc * kTargets + tg];
+        long long acc = 0;
+        int v = 0;
+        for (; v < 255; ++v) { acc += h[v]; if (acc > st.rank) break; }
+        st.value = __fdiv_rn((float)v, 255.0f);                    // img = frame.astype(float32) / 255.0
+    }
+}
+
+__global__ void __launch_bounds__(NT) vgg_enhance_u8_kernel(const uint8_t* __restrict__ frames, float* __restrict__ out, long long n,
+                                                            const SelState* __restrict__ state, const EnhanceParams* __restrict__ prm) {
+    const int b = blockIdx.y;
+    __shared__ float lo[3], rng[3], sval[256];
+    if (threadIdx.x < 3) {
+        const float p_lo = state[(b * 3 + threadIdx.x) * kTargets + 0].value;
+        const float p_hi = state[(b * 3 + threadIdx.x) * kTargets + 1].value;
+        lo[threadIdx.x] = p_lo;
+        rng[threadIdx.x] = __fadd_rn(__fsub_rn(p_hi, p_lo), 1e-8f);
+    }
+    for (int i = threadIdx.x; i < 256; i += NT) sval[i] = __fdiv_rn((float)i, 255.0f);
+    __syncthreads();
+    const float omega = prm[b].omega, gamma = prm[b].gamma;
+    const uint8_t* f = frames + (size_t)b * 3 * n;
+    float* o = out + (size_t)b * 3 * n;
+    const bool vec = (n & 3) == 0 && (reinterpret_cast<uintptr_t>(f) & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
+    if (vec) {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(f);
+        for (long long g = (long long)blockIdx.x * NT + threadIdx.x; g < n / 4; g += (long long)gridDim.x * NT) {
+            const uint32_t w0 = __ldg(w + 3 * g), w1 = __ldg(w + 3 * g + 1), w2 = __ldg(w + 3 * g + 2);
+            float4 r, gg, bl;
+            r.x = sval[w0 & 255]; gg.x = sval[(w0 >> 8) & 255]; bl.x = sval[(w0 >> 16) & 255];
+            r.y = sval[w0 >> 24]; gg.y = sval[w1 & 255]; bl.y = sval[(w1 >> 8) & 255];
+            r.z = sval[(w1 >> 16) & 255]; gg.z = sval[w1 >> 24]; bl.z = sval[w2 & 255];
+            r.w = sval[(w2 >> 8) & 255]; gg.w = sval[(w2 >> 16) & 255]; bl.w = sval[w2 >> 24];
+            enhance_pixel(r.x, gg.x, bl.x, lo, rng, true, omega, true, gamma);
+            enhance_pixel(r.y, gg.y, bl.y, lo, rng, true, omega, true, gamma);
+            enhance_pixel(r.z, gg.z, bl.z, lo, rng, true, omega, true, gamma);
+            enhance_pixel(r.w, gg.w, bl.w, lo, rng, true, omega, true, gamma);
+            __stcs(reinterpret_cast<float4*>(o) + g, r);
+            __stcs(reinterpret_cast<float4*>(o + n) + g, gg);
+            __stcs(reinterpret_cast<float4*>(o + 2 * n) + g, bl);
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < n; i += (long long)gridDim.x * NT) {
+            float r = sval[f[3 * i]], g = sval[f[3 * i + 1]], bl = sval[f[3 * i + 2]];
+            enhance_pixel(r, g, bl, lo, rng, true, omega, true, gamma);
+            o[i] = r; o[n + i] = g; o[2 * n + i] = bl;
+        }
+    }
+}
+
 // device-resident parameters (the network's outputs): ranks int(L / 100.0 * n) in double arithmetic (VGG:78-82),
 // clamped like use_trained_model.py:74-79 when `clamp_ranges` is set
 __global__ void vgg_params_kernel(const float* __restrict__ p /* [4][batch]: L_low, L_high, omega, gamma */, int batch,
@@ -505,6 +564,27 @@ int uwie_vgg_enhance_dev(const float* img_dev, int batch, int height, int width,
     vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
     vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist);
     vgg_enhance_kernel<<<dim3(grid_for(n / 4 + 1), batch), NT, 0, st>>>(img_dev, out_dev, n, state, prm, 1, 1);
+    CUV(cudaGetLastError());
+    return UWIE_OK;
+}
+
+int uwie_vgg_enhance_u8(const uint8_t* frames_dev, int batch, int height, int width, const float* params_dev, int clamp_ranges,
+                        float* used_dev, float* out_dev, void* workspace_dev, size_t workspace_bytes, void* stream) {
+    if (!frames_dev || !out_dev || !params_dev || batch < 1 || height < 1 || width < 1)
+        return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance_u8: bad arguments");
+    const VggLayout L = vgg_layout(batch);
+    if (!workspace_dev || workspace_bytes < L.total) return uwie_fail(UWIE_ERR_ARG, "uwie_vgg_enhance_u8: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)workspace_dev;
+    const long long n = (long long)height * width;
+    SelState* state = (SelState*)(ws + L.state);
+    EnhanceParams* prm = (EnhanceParams*)(ws + L.prm);
+    unsigned* hist = (unsigned*)(ws + L.hist);
+    vgg_params_kernel<<<(batch + 127) / 128, 128, 0, st>>>(params_dev, batch, n, clamp_ranges, state, prm, used_dev);
+    CUV(cudaMemsetAsync(hist, 0, (size_t)batch * 768 * 4, st));
+    launch_frame_hist(frames_dev, batch, height, width, hist, st);
+    vgg_ranks_u8_kernel<<<(batch * 3 + 127) / 128, 128, 0, st>>>(hist, batch, state);
+    vgg_enhance_u8_kernel<<<dim3(grid_for(n / 4 + 1), batch), NT, 0, st>>>(frames_dev, out_dev, n, state, prm);
     CUV(cudaGetLastError());
     return UWIE_OK;
 }

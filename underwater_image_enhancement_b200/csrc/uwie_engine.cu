@@ -6,7 +6,10 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <array>
 #include <cstring>
+#include <map>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -91,6 +94,15 @@ struct uwie_engine {
         uwie_engine* twin = nullptr; bool twin_failed = false;
         cudaStream_t s_run2 = nullptr; cudaEvent_t ev_twin = nullptr;
     } pipe;
+    // CUDA graphs of the kernel sequence, one per (batch, pointer set): a step of the bench or of the host pipeline
+    // presents the same few pointer sets again and again (chunk slices / the two slots), so the ~60 launches of a
+    // call are replayed as ONE graph launch.  First sight of a pointer set runs eagerly, the second captures.
+    typedef std::array<uintptr_t, 9> GraphKey;
+    struct GraphExec { cudaGraphExec_t exec; int launches; };
+    std::map<GraphKey, GraphExec> graphs;
+    std::set<GraphKey> seen;
+    bool use_graphs = true;
+    long long graph_replays = 0;
     uwie_library pub_lib;                         // what the engine was created from (for the twin)
     std::vector<uwie_strategy> pub_strategies;
     template <class T> T* at(size_t off) const { return reinterpret_cast<T*>(ws + off); }
@@ -363,10 +375,12 @@ void uwie_engine_destroy(uwie_engine* e) {
     }
     for (auto& m : e->marks) cudaEventDestroy(m.ev);
     for (auto& ev : e->ev_pool) cudaEventDestroy(ev);
+    for (auto& g : e->graphs) cudaGraphExecDestroy(g.second.exec);
     delete e;
 }
 
 int uwie_engine_last_launches(const uwie_engine* e) { return e ? e->last_launches : 0; }
+long long uwie_engine_graph_replays(const uwie_engine* e) { return e ? e->graph_replays + (e->pipe.twin ? e->pipe.twin->graph_replays : 0) : 0; }
 
 }  // extern "C"
 
@@ -562,6 +576,47 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     return UWIE_OK;
 }
 
+// enqueue_batch through the graph cache (see uwie_engine::graphs).  Streams that cannot be captured (the legacy and
+// per-thread default streams), profiling runs and UWIE_NO_GRAPH=1 take the eager path.
+int run_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out_all, uint8_t* out_best, double* scores,
+              int32_t* best, int32_t* types, float* light, cudaStream_t st) {
+    static const bool disabled = std::getenv("UWIE_NO_GRAPH") != nullptr;
+    const bool capturable = st != nullptr && st != cudaStreamLegacy && st != cudaStreamPerThread;
+    if (disabled || !e->use_graphs || e->prof_on || !capturable)
+        return enqueue_batch(e, frames, batch, out_all, out_best, scores, best, types, light, st);
+    const uwie_engine::GraphKey key = {(uintptr_t)frames, (uintptr_t)out_all, (uintptr_t)out_best, (uintptr_t)scores,
+                                       (uintptr_t)best, (uintptr_t)types, (uintptr_t)light, (uintptr_t)batch, 0};
+    auto it = e->graphs.find(key);
+    if (it != e->graphs.end()) {
+        CU(cudaGraphLaunch(it->second.exec, st));
+        e->last_launches = it->second.launches;
+        ++e->graph_replays;
+        return UWIE_OK;
+    }
+    if (e->seen.insert(key).second || e->graphs.size() >= 64)          // first sight (or cache full): eager
+        return enqueue_batch(e, frames, batch, out_all, out_best, scores, best, types, light, st);
+    if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError();
+        e->use_graphs = false;
+        return enqueue_batch(e, frames, batch, out_all, out_best, scores, best, types, light, st);
+    }
+    const int rc = enqueue_batch(e, frames, batch, out_all, out_best, scores, best, types, light, st);
+    cudaGraph_t g = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(st, &g);
+    cudaGraphExec_t exec = nullptr;
+    if (rc == UWIE_OK && ce == cudaSuccess && g && cudaGraphInstantiate(&exec, g, 0) == cudaSuccess) {
+        cudaGraphDestroy(g);
+        e->graphs[key] = {exec, e->last_launches};
+        CU(cudaGraphLaunch(exec, st));
+        ++e->graph_replays;
+        return UWIE_OK;
+    }
+    if (g) cudaGraphDestroy(g);
+    cudaGetLastError();
+    e->use_graphs = false;                                            // capture is not possible here: stay eager
+    return enqueue_batch(e, frames, batch, out_all, out_best, scores, best, types, light, st);
+}
+
 }  // namespace
 
 extern "C" {
@@ -571,8 +626,8 @@ int uwie_enhance_score(uwie_engine* e, const uint8_t* frames_dev, int batch, uin
                        float* light_dev, void* stream) {
     if (!e || !frames_dev) return fail(UWIE_ERR_ARG, "null engine or frames");
     if (batch < 1 || batch > e->B) return fail(UWIE_ERR_ARG, "batch must be in [1, max_batch]");
-    return enqueue_batch(e, frames_dev, batch, out_all_dev, out_best_dev, scores_dev, best_dev, type_dev,
-                         light_dev, static_cast<cudaStream_t>(stream));
+    return run_batch(e, frames_dev, batch, out_all_dev, out_best_dev, scores_dev, best_dev, type_dev,
+                     light_dev, static_cast<cudaStream_t>(stream));
 }
 
 // detect_image_type (six_stadigy.py:292-302) of a batch: channel histograms + the colour-cast set-up kernel only.
@@ -706,8 +761,8 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
         cudaStream_t ls = (two_lanes && k) ? hp.s_run2 : st;
         CU(cudaStreamWaitEvent(ls, hp.ev_in[k], 0));
         if (chunk >= 2) CU(cudaStreamWaitEvent(ls, hp.ev_out[k], 0));
-        int rc = enqueue_batch(lane, hp.frames[k], nb, out_all_host ? hp.out_all[k] : nullptr,
-                               out_best_host ? hp.best_img[k] : nullptr, d_scores, d_best, d_types, d_light, ls);
+        int rc = run_batch(lane, hp.frames[k], nb, out_all_host ? hp.out_all[k] : nullptr,
+                           out_best_host ? hp.best_img[k] : nullptr, d_scores, d_best, d_types, d_light, ls);
         if (rc) return rc;
         launches_total += lane->last_launches;
         CU(cudaEventRecord(hp.ev_run[k], ls));

@@ -123,6 +123,11 @@ class Engine:
     def last_launches(self) -> int:
         return int(self._lib.uwie_engine_last_launches(self._h))
 
+    @property
+    def graph_replays(self) -> int:
+        """Calls served by replaying a captured CUDA graph of the kernel sequence (uwie_engine_graph_replays)."""
+        return int(self._lib.uwie_engine_graph_replays(self._h))
+
     # ------------------------------------------------------------------ host path (C ABI with host buffers)
     def run_host(self, frames: np.ndarray, want_all=True, want_best=False, out_all=None, out_best=None):
         frames = np.ascontiguousarray(frames, dtype=np.uint8)

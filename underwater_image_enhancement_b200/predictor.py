@@ -8,7 +8,8 @@ around it runs in libuwie_b200.so on whole batches and without host round trips:
       -> uwie_vgg_features_u8   18 statistics zero-padded to 79            (vgg_16_UIE.py:435-466)
       -> uwie_vgg_preprocess_u8 224x224 fixed-point resize + normalisation (use_trained_model.py:39-46)
       -> network (PyTorch)      {omega, gamma, L_low, L_high} as [B,1] tensors, left on the device
-      -> uwie_vgg_enhance_dev   safety clamps of UTM:74-79, order statistics, stretch, dehaze, gamma on the device
+      -> uwie_vgg_enhance_u8    safety clamps of UTM:74-79, order statistics from the byte histograms, stretch, dehaze,
+                                gamma on the device; float32 NCHW out
 
 The reference's per-image API (predict_parameters -> dict of floats, enhance_image -> float32 HWC array,
 process_single_image, process_folder) is kept on top of the batched calls.
@@ -88,8 +89,7 @@ class EnhancementPredictor:
         frames = self._frames(frames)
         if params_dev is None:
             params_dev = self.predict_parameters_batch(frames)
-        img = (frames.permute(0, 3, 1, 2).to(torch.float32) / 255.0).contiguous()      # UTM:48-51, 119
-        return self.enhancer.forward_dev(img, params_dev, clamp_ranges=True)
+        return vgg.enhance_frames_u8(frames, params_dev, clamp_ranges=True)              # frame / 255 (UTM:119) inside
 
     # ------------------------------------------------------------------ the reference's per-image API
     def predict_parameters(self, img):

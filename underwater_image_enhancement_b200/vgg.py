@@ -108,6 +108,28 @@ class DifferentiableEnhancement:
         return out, used
 
 
+def enhance_frames_u8(frames: torch.Tensor, params_dev: torch.Tensor, clamp_ranges: bool = False):
+    """uint8 CUDA frames [B, H, W, 3] -> (float32 [B, 3, H, W] enhanced, float32 [4, B] parameters applied): the
+    enhancement of frame / 255 with device-resident parameters, reading the frame as bytes (uwie_vgg_enhance_u8)."""
+    if not (frames.is_cuda and params_dev.is_cuda and frames.dtype == torch.uint8):
+        raise ValueError("frames must be a uint8 CUDA tensor and params_dev a CUDA tensor")
+    frames = frames.contiguous()
+    B, H, W, _ = frames.shape
+    params_dev = params_dev.to(torch.float32).contiguous()
+    if tuple(params_dev.shape) != (4, B):
+        raise ValueError(f"params_dev must be [4, {B}], got {tuple(params_dev.shape)}")
+    out = torch.empty((B, 3, H, W), dtype=torch.float32, device=frames.device)
+    used = torch.empty_like(params_dev)
+    ws, need = _workspace(B, frames.device)
+    with torch.cuda.device(frames.device):
+        _lib.check(_lib.load().uwie_vgg_enhance_u8(C.c_void_p(frames.data_ptr()), B, H, W, C.c_void_p(params_dev.data_ptr()),
+                                                   int(bool(clamp_ranges)), C.c_void_p(used.data_ptr()),
+                                                   C.c_void_p(out.data_ptr()), C.c_void_p(ws.data_ptr()), need,
+                                                   _stream(frames.device)))
+    ws.record_stream(torch.cuda.current_stream(frames.device))
+    return out, used
+
+
 def _frames_u8(img, device):
     """HWC or BHWC uint8 image(s), NumPy or torch -> contiguous CUDA uint8 [B,H,W,3]."""
     t = torch.as_tensor(img) if not isinstance(img, torch.Tensor) else img
