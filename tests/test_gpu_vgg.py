@@ -110,7 +110,9 @@ def test_enhance_from_bytes_equals_enhance_of_float_image(cuda_device):
     d = torch.from_numpy(frames).cuda()
     params = torch.tensor([[0.5, 12.0, 40.0], [99.5, 90.0, 60.0], [0.05, 0.6, 0.95], [0.4, 1.2, 3.5]], device="cuda")
     out8, used8 = vgg.enhance_frames_u8(d, params, clamp_ranges=True)
-    img = (d.permute(0, 3, 1, 2).float() / 255.0).contiguous()
+    # frame.astype(np.float32) / 255.0 on the host, as the reference does (use_trained_model.py:119): torch's CUDA division by
+    # a scalar multiplies by the reciprocal and is 1 ulp off for some bytes
+    img = torch.from_numpy(np.ascontiguousarray((frames.astype(np.float32) / 255.0).transpose(0, 3, 1, 2))).cuda()
     outf, usedf = vgg.DifferentiableEnhancement().forward_dev(img, params, clamp_ranges=True)
     assert torch.equal(used8, usedf)
     assert torch.equal(used8.cpu(), torch.tensor([[1.0, 12.0, 30.0], [99.0, 90.0, 65.0], [0.1, 0.6, 0.9], [0.5, 1.2, 3.0]]))

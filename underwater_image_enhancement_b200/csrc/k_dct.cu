@@ -103,10 +103,12 @@ __device__ __forceinline__ void gemm_tile(int M, int N, int K, int m0, int n0, b
 #pragma unroll
         for (int kk = 0; kk < BK; ++kk) {
             float a[TM], b[TN];
-            const float4 a0 = *reinterpret_cast<const float4*>(&sA[buf][kk][ty * 8]);
-            const float4 a1 = *reinterpret_cast<const float4*>(&sA[buf][kk][ty * 8 + 4]);
-            const float4 b0 = *reinterpret_cast<const float4*>(&sB[buf][kk][tx * 8]);
-            const float4 b1 = *reinterpret_cast<const float4*>(&sB[buf][kk][tx * 8 + 4]);
+            // a thread's 8 rows / columns are two groups of 4, 64 apart: the 16 lanes of a row of threads then read 16
+            // consecutive float4 (256 contiguous bytes) instead of every other one: no shared-memory bank conflicts
+            const float4 a0 = *reinterpret_cast<const float4*>(&sA[buf][kk][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&sA[buf][kk][64 + ty * 4]);
+            const float4 b0 = *reinterpret_cast<const float4*>(&sB[buf][kk][tx * 4]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&sB[buf][kk][64 + tx * 4]);
             a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
             b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
 #pragma unroll
@@ -124,7 +126,7 @@ __device__ __forceinline__ void gemm_tile(int M, int N, int K, int m0, int n0, b
     for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < TN; ++j) {
-            const int m = m0 + ty * 8 + i, n = n0 + tx * 8 + j;
+            const int m = m0 + ty * 4 + (i & 3) + (i >> 2) * 64, n = n0 + tx * 4 + (j & 3) + (j >> 2) * 64;
             if (m < M && n < N) epi(m, n, acc[i][j]);
         }
 }
