@@ -299,7 +299,7 @@ int uwie_prim_gamma(const void* img_dev, int dtype, size_t count, double exponen
 /* color_correction (SS:305-323): clip(img * scale3[c], 0, 1); scale3 is a HOST array. */
 int uwie_prim_scale_clip(const void* img_dev, int dtype, int height, int width, const double* scale3, void* out_dev, void* stream);
 
-/* Channel means of a float image (detect_image_type, SS:292-302): 3 float64 on the device.  Workspace: 512 bytes. */
+/* Channel means of a float image (detect_image_type, SS:292-302): 3 float64 on the device.  Workspace: 4096 bytes. */
 int uwie_prim_channel_means(const void* img_dev, int dtype, int height, int width, double* means_dev, void* workspace_dev,
                             size_t workspace_bytes, void* stream);
 

@@ -172,3 +172,47 @@ def preset(library_id: int):
     if n < 0:
         check(n)
     return lib, [arr[i] for i in range(n)]
+
+
+# ---------------------------------------------------------------------------------------------
+# Scratch memory for the entry points.  Two test hooks replace the tools this GPU pool keeps closed (compute-sanitizer):
+#   UWIE_POISON=<0..255>   every scratch buffer is filled with that byte before use: results must not depend on
+#                          uninitialised scratch (initcheck's job);
+#   UWIE_GUARD=<bytes>     every scratch buffer gets that many canary bytes before and after it; guards_intact() tells
+#                          whether any kernel wrote outside what the *_workspace_bytes functions promised (memcheck's job).
+# Both are off in normal use and cost nothing then.
+# ---------------------------------------------------------------------------------------------
+_CANARY = 0xC3
+_GUARDED = []
+
+
+def scratch(nbytes: int, device):
+    import torch
+    nbytes = max(int(nbytes), 256)
+    guard = int(os.environ.get("UWIE_GUARD", "0") or 0)
+    guard = (guard + 255) & ~255
+    poison = os.environ.get("UWIE_POISON", "")
+    if not guard and poison == "":
+        return torch.empty(nbytes, dtype=torch.uint8, device=device)
+    padded = (nbytes + 255) & ~255
+    whole = torch.empty(padded + 2 * guard, dtype=torch.uint8, device=device)
+    if guard:
+        whole[:guard] = _CANARY
+        whole[guard + padded:] = _CANARY
+        _GUARDED.append((whole, guard, padded))
+    inner = whole[guard:guard + nbytes]
+    if poison != "":
+        whole[guard:guard + padded] = int(poison) & 255
+    return inner
+
+
+def guards_intact(clear: bool = True) -> bool:
+    """True when no canary byte around any scratch buffer handed out since the last call was overwritten."""
+    import torch
+    ok = True
+    for whole, guard, padded in _GUARDED:
+        torch.cuda.synchronize(whole.device)
+        ok = ok and bool((whole[:guard] == _CANARY).all()) and bool((whole[guard + padded:] == _CANARY).all())
+    if clear:
+        _GUARDED.clear()
+    return ok

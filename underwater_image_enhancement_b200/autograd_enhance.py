@@ -32,7 +32,7 @@ class EnhanceFunction(torch.autograd.Function):
         B, _, H, W = img.shape
         params = torch.stack([l_low.detach(), l_high.detach(), omega.detach(), gamma.detach()]).contiguous()
         need = lib.uwie_vgg_workspace_bytes(B)
-        ws = torch.empty(need, dtype=torch.uint8, device=img.device)
+        ws = _lib.scratch(need, img.device)
         out = torch.empty_like(img)
         stream = C.c_void_p(torch.cuda.current_stream(img.device).cuda_stream)
         with torch.cuda.device(img.device):

@@ -28,10 +28,15 @@ namespace uwie {
 
 namespace {
 
-constexpr int GC = 5;                 // columns per lane (odd: conflict-free 64-bit shared accesses)
+// Columns per lane (odd: conflict-free 64-bit shared accesses).  Measured in round 2: 3 columns per lane (80 registers,
+// three blocks = 24 warps per SM, but 96 - r + 1 outputs of 96 columns instead of 160 - r + 1 of 160 and the per-row
+// shuffles / loop overhead spread over fewer pixels) is SLOWER than 5 (128 registers, 14 warps): 44.9 vs 32.1 ms per
+// 256-frame step.
+constexpr int GC = 5;
 constexpr int GSPAN = 32 * GC;        // columns a warp carries, outputs = GSPAN - r + 1
 constexpr int GWARPS = 8;
 constexpr int GNT = 32 * GWARPS;
+constexpr int GBLOCKS_PER_SM = GC <= 3 ? 3 : 2;
 
 // ------------------------------------------------------------------ gray + dark channel records
 __global__ void __launch_bounds__(256) gf_prep_kernel(GuidedArgs a) {
@@ -82,7 +87,7 @@ __device__ __forceinline__ Strip make_strip(const GuidedArgs& a, int r) {
 
 // ------------------------------------------------------------------ a, b
 template <bool CLIP, bool FAST>
-__global__ void __launch_bounds__(GNT, 2) gf_ab_kernel(GuidedArgs a) {
+__global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a) {
     __shared__ double sP[GWARPS][GSPAN];
     __shared__ double sGP[GWARPS][GSPAN];
     __shared__ unsigned long long sG[GWARPS][GSPAN];     // (sum g) << 32 | sum g*g
@@ -209,7 +214,7 @@ struct RecoverShared {
     unsigned shist[3 * kSelBinsA];
 };
 template <class T>
-__global__ void __launch_bounds__(GNT, 2) gf_recover_kernel(GuidedArgs a) {
+__global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_recover_kernel(GuidedArgs a) {
     // dynamic shared memory (57 KB, above the static limit), see RecoverShared
     extern __shared__ __align__(16) unsigned char gf_smem[];
     RecoverShared& sm = *reinterpret_cast<RecoverShared*>(gf_smem);
@@ -401,21 +406,32 @@ int selftest_division(unsigned long long count, unsigned long long seed, unsigne
     return rc == cudaSuccess ? 0 : 1;
 }
 
-int launch_guided(const GuidedArgs& a, int max_radius, cudaStream_t st) {
-    if (a.n_dehaze == 0) return 0;
+int launch_guided(const GuidedArgs& a0, int max_radius, cudaStream_t st) {
+    if (a0.n_dehaze == 0) return 0;
+    GuidedArgs a = a0;
     const int inst = a.B * a.n_dehaze;
     const size_t npix = (size_t)a.H * a.W;
     int pb = (int)((npix + 256 * 8 - 1) / (256 * 8));
     if (pb > 148 * 8) pb = 148 * 8;
     gf_prep_kernel<<<dim3(pb, a.B), 256, 0, st>>>(a);
-    const int chunks = (a.H + a.rows_per_block - 1) / a.rows_per_block;
     // strips are sized by each instance's own radius; the grid covers the largest radius present
     // (fewest outputs per strip); for a smaller radius the surplus warps exit at once.
-    // Warps per block: the strips spread evenly over the fewest blocks (1920 columns: 14 strips = 2 x 7 warps)
+    // Warps per block: the strips spread evenly over the fewest blocks (1920 columns, r = 20: 25 strips = 4 x 7 warps)
     const int outw_min = GSPAN - max_radius + 1;
     const int strips = (a.W + outw_min - 1) / outw_min;
     const int bx = (strips + GWARPS - 1) / GWARPS;
     const int nt = 32 * ((strips + bx - 1) / bx);
+    // row chunks: every chunk re-reads r - 1 warm-up rows, so as few as fill the machine ONCE
+    // (all blocks do the same work, a second partial wave would only be a tail)
+    {
+        const int per_chunk = bx * inst;
+        int chunks = (148 * GBLOCKS_PER_SM) / (per_chunk > 0 ? per_chunk : 1);
+        const int most = a.H / (3 * (max_radius > 0 ? max_radius : 1));
+        if (chunks > most) chunks = most;
+        if (chunks < 1) chunks = 1;
+        a.rows_per_block = (a.H + chunks - 1) / chunks;
+    }
+    const int chunks = (a.H + a.rows_per_block - 1) / a.rows_per_block;
     dim3 grid(bx, chunks, inst);
     if (a.lib.clip_t0) {
         if (a.eps_safe) gf_ab_kernel<true, true><<<grid, nt, 0, st>>>(a);

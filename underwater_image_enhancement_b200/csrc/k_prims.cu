@@ -407,16 +407,21 @@ __global__ void quantise_kernel(const T* __restrict__ img, size_t n, uint8_t* __
     }
 }
 
-// per-channel sums of a rectangle (float64 accumulation): out[c] += sum, out[3 + c] += sum of squares about mean[c]
+// per-channel sums of a rectangle (float64 accumulation) as per-block partials part[q][block][c] (sum, or sum of squares
+// about mean[q][c]); stats_reduce_kernel adds them in block order, so the result does not depend on scheduling
+constexpr int kStatBlocks = 64;
 template <class T, bool SECOND>
 __global__ void __launch_bounds__(256) rect_stats_kernel(const T* __restrict__ img, int W, const QuadRect* rect, int quadrants,
-                                                         const double* __restrict__ mean, double* __restrict__ out) {
+                                                         const double* __restrict__ mean, double* __restrict__ part) {
     // blockIdx.y = quadrant (or 0 when quadrants == 0: the whole rectangle)
     const QuadRect r = *rect;
     int y0 = r.y0, y1 = r.y1, x0 = r.x0, x1 = r.x1;
     const int q = blockIdx.y;
     if (quadrants) {
-        if (!r.active) return;
+        if (!r.active) {
+            if (threadIdx.x < 3) part[((size_t)q * kStatBlocks + blockIdx.x) * 3 + threadIdx.x] = 0.0;
+            return;
+        }
         const int ym = r.y0 + (r.y1 - r.y0) / 2, xm = r.x0 + (r.x1 - r.x0) / 2;
         y0 = (q & 2) ? ym : r.y0; y1 = (q & 2) ? r.y1 : ym;
         x0 = (q & 1) ? xm : r.x0; x1 = (q & 1) ? r.x1 : xm;
@@ -443,8 +448,16 @@ __global__ void __launch_bounds__(256) rect_stats_kernel(const T* __restrict__ i
     if (threadIdx.x < 3) {
         double v = 0;
         for (int w = 0; w < 8; ++w) v += red[w][threadIdx.x];
-        atomicAdd(&out[q * 3 + threadIdx.x], v);
+        part[((size_t)q * kStatBlocks + blockIdx.x) * 3 + threadIdx.x] = v;
     }
+}
+__global__ void stats_reduce_kernel(const double* __restrict__ part, int nblocks, int nq, double* __restrict__ out) {
+    const int i = threadIdx.x;                       // q * 3 + c
+    if (i >= nq * 3) return;
+    const int q = i / 3, c = i - q * 3;
+    double v = 0;
+    for (int b = 0; b < nblocks; ++b) v += part[((size_t)q * kStatBlocks + b) * 3 + c];
+    out[i] = v;
 }
 
 // sums -> means (per quadrant), and zero the second-pass accumulators
@@ -810,12 +823,13 @@ int uwie_prim_quantise(const void* img_dev, int dtype, size_t count, uint8_t* ou
 }
 
 namespace {
-struct LightLayout { size_t q, cast, rect, sums, ssq, means, counts, quad_hist, trace, labels, tile_list, tile_n, total; };
+struct LightLayout { size_t q, cast, rect, sums, ssq, means, part, counts, quad_hist, trace, labels, tile_list, tile_n, total; };
 LightLayout light_layout(int H, int W) {
     Bump b; LightLayout L;
     const size_t N = (size_t)H * W;
     L.q = b.take(N * 3); L.cast = b.take(sizeof(CastTables)); L.rect = b.take(sizeof(QuadRect));
     L.sums = b.take(12 * 8); L.ssq = b.take(12 * 8); L.means = b.take(12 * 8);
+    L.part = b.take((size_t)4 * kStatBlocks * 3 * 8);
     L.counts = b.take(kQuadLevelsMax * 4 * 4); L.quad_hist = b.take((size_t)kQuadLevelsMax * 4 * 768 * 4);
     L.trace = b.take(kQuadLevelsMax * 4 * 8);
     L.labels = b.take(N * 4);
@@ -865,16 +879,20 @@ int uwie_prim_atmospheric_light(const void* img_dev, int dtype, int height, int 
         rows = rows - rows / 2; cols = cols - cols / 2;
         ca.level = level;
         launch_canny(ca, rows, cols, 4, st);
-        const int gx = grid_for((size_t)rows * cols, 256, 148);
+        const int gx = grid_for((size_t)rows * cols, 256, kStatBlocks);
+        double* part = reinterpret_cast<double*>(ws + L.part);
         if (dtype == 1) {
-            rect_stats_kernel<float, false><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const float*>(img_dev), width, rect, 1, nullptr, sums);
+            rect_stats_kernel<float, false><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const float*>(img_dev), width, rect, 1, nullptr, part);
+            stats_reduce_kernel<<<1, 32, 0, st>>>(part, gx, 4, sums);
             quad_means_kernel<<<1, 32, 0, st>>>(rect, sums, means, ssq);
-            rect_stats_kernel<float, true><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const float*>(img_dev), width, rect, 1, means, ssq);
+            rect_stats_kernel<float, true><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const float*>(img_dev), width, rect, 1, means, part);
         } else {
-            rect_stats_kernel<double, false><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const double*>(img_dev), width, rect, 1, nullptr, sums);
+            rect_stats_kernel<double, false><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const double*>(img_dev), width, rect, 1, nullptr, part);
+            stats_reduce_kernel<<<1, 32, 0, st>>>(part, gx, 4, sums);
             quad_means_kernel<<<1, 32, 0, st>>>(rect, sums, means, ssq);
-            rect_stats_kernel<double, true><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const double*>(img_dev), width, rect, 1, means, ssq);
+            rect_stats_kernel<double, true><<<dim3(gx, 4), 256, 0, st>>>(static_cast<const double*>(img_dev), width, rect, 1, means, part);
         }
+        stats_reduce_kernel<<<1, 32, 0, st>>>(part, gx, 4, ssq);
         quad_descend_float_kernel<<<1, 32, 0, st>>>(rect, sums, ssq, counts, level, reinterpret_cast<double*>(ws + L.trace), sums);
         ++level;
     }
@@ -885,12 +903,13 @@ int uwie_prim_atmospheric_light(const void* img_dev, int dtype, int height, int 
 }
 
 namespace {
-struct ScoreLayout { size_t q, gray, rect, sums, ssq, means, count, labels, tile_list, tile_n, total; };
+struct ScoreLayout { size_t q, gray, rect, sums, ssq, means, part, count, labels, tile_list, tile_n, total; };
 ScoreLayout score_layout(int H, int W) {
     Bump b; ScoreLayout L;
     const size_t N = (size_t)H * W;
     L.q = b.take(N * 3); L.gray = b.take(N); L.rect = b.take(sizeof(QuadRect));
-    L.sums = b.take(12 * 8); L.ssq = b.take(12 * 8); L.means = b.take(12 * 8); L.count = b.take(256);
+    L.sums = b.take(12 * 8); L.ssq = b.take(12 * 8); L.means = b.take(12 * 8);
+    L.part = b.take((size_t)kStatBlocks * 3 * 8); L.count = b.take(256);
     L.labels = b.take(N * 4);
     const size_t slots = canny_tile_slots(H, W, 1);
     L.tile_list = b.take(slots * kCannyListCap * sizeof(int2)); L.tile_n = b.take(slots * 4);
@@ -927,16 +946,20 @@ int uwie_prim_region_score(const void* img_dev, int dtype, int height, int width
     if (rc) return rc;
     gray_from_bytes_kernel<<<grid_for(N), 256, 0, st>>>(q, N, gray);
     const QuadRect* rect = reinterpret_cast<QuadRect*>(ws + L.rect);
-    const int gx = grid_for(N, 256, 148 * 2);
+    const int gx = grid_for(N, 256, kStatBlocks);
+    double* part = reinterpret_cast<double*>(ws + L.part);
     if (dtype == 1) {
-        rect_stats_kernel<float, false><<<dim3(gx, 1), 256, 0, st>>>((const float*)img_dev, width, rect, 0, nullptr, sums);
+        rect_stats_kernel<float, false><<<dim3(gx, 1), 256, 0, st>>>((const float*)img_dev, width, rect, 0, nullptr, part);
+        stats_reduce_kernel<<<1, 32, 0, st>>>(part, gx, 1, sums);
         means3_kernel<<<1, 32, 0, st>>>(sums, (double)N, means, ssq);
-        rect_stats_kernel<float, true><<<dim3(gx, 1), 256, 0, st>>>((const float*)img_dev, width, rect, 0, means, ssq);
+        rect_stats_kernel<float, true><<<dim3(gx, 1), 256, 0, st>>>((const float*)img_dev, width, rect, 0, means, part);
     } else {
-        rect_stats_kernel<double, false><<<dim3(gx, 1), 256, 0, st>>>((const double*)img_dev, width, rect, 0, nullptr, sums);
+        rect_stats_kernel<double, false><<<dim3(gx, 1), 256, 0, st>>>((const double*)img_dev, width, rect, 0, nullptr, part);
+        stats_reduce_kernel<<<1, 32, 0, st>>>(part, gx, 1, sums);
         means3_kernel<<<1, 32, 0, st>>>(sums, (double)N, means, ssq);
-        rect_stats_kernel<double, true><<<dim3(gx, 1), 256, 0, st>>>((const double*)img_dev, width, rect, 0, means, ssq);
+        rect_stats_kernel<double, true><<<dim3(gx, 1), 256, 0, st>>>((const double*)img_dev, width, rect, 0, means, part);
     }
+    stats_reduce_kernel<<<1, 32, 0, st>>>(part, gx, 1, ssq);
     CannyArgs ca;
     std::memset(&ca, 0, sizeof(ca));
     ca.mode = CANNY_PLANES; ca.H = height; ca.W = width; ca.low = 50; ca.high = 150;
@@ -1144,17 +1167,18 @@ int uwie_prim_scale_clip(const void* img_dev, int dtype, int height, int width, 
 // channel means of a float image (detect_image_type, six_stadigy.py:292-302): means_dev receives 3 float64
 int uwie_prim_channel_means(const void* img_dev, int dtype, int height, int width, double* means_dev, void* workspace_dev,
                             size_t workspace_bytes, void* stream) {
-    if (!img_dev || !means_dev || !workspace_dev || (dtype != 1 && dtype != 2) || workspace_bytes < 512)
-        return uwie_fail(UWIE_ERR_ARG, "channel_means: bad arguments (workspace of 512 bytes)");
+    if (!img_dev || !means_dev || !workspace_dev || (dtype != 1 && dtype != 2) || workspace_bytes < 4096)
+        return uwie_fail(UWIE_ERR_ARG, "channel_means: bad arguments (workspace of 4096 bytes)");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     QuadRect r; r.y0 = 0; r.y1 = height; r.x0 = 0; r.x1 = width; r.active = 1; r.level = 0;
     char* ws = static_cast<char*>(workspace_dev);
     double* sums = reinterpret_cast<double*>(ws + 256);
+    double* part = reinterpret_cast<double*>(ws + 512);                     // kStatBlocks x 3 doubles = 1536 bytes
     PCU(cudaMemcpyAsync(ws, &r, sizeof(r), cudaMemcpyHostToDevice, st));
-    PCU(cudaMemsetAsync(sums, 0, 12 * 8, st));
-    const int gx = grid_for((size_t)height * width, 256, 148 * 2);
-    if (dtype == 1) rect_stats_kernel<float, false><<<dim3(gx, 1), 256, 0, st>>>((const float*)img_dev, width, reinterpret_cast<QuadRect*>(ws), 0, nullptr, sums);
-    else rect_stats_kernel<double, false><<<dim3(gx, 1), 256, 0, st>>>((const double*)img_dev, width, reinterpret_cast<QuadRect*>(ws), 0, nullptr, sums);
+    const int gx = grid_for((size_t)height * width, 256, kStatBlocks);
+    if (dtype == 1) rect_stats_kernel<float, false><<<dim3(gx, 1), 256, 0, st>>>((const float*)img_dev, width, reinterpret_cast<QuadRect*>(ws), 0, nullptr, part);
+    else rect_stats_kernel<double, false><<<dim3(gx, 1), 256, 0, st>>>((const double*)img_dev, width, reinterpret_cast<QuadRect*>(ws), 0, nullptr, part);
+    stats_reduce_kernel<<<1, 32, 0, st>>>(part, gx, 1, sums);
     divide3_kernel<<<1, 32, 0, st>>>(sums, (double)height * (double)width, means_dev);
     PCU(cudaGetLastError());
     return UWIE_OK;

@@ -476,18 +476,7 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
         ga.B = batch; ga.S = S; ga.H = H; ga.W = W; ga.lib = e->lib; ga.recipes = sa.recipes;
         ga.n_dehaze = e->n_dehaze;
         for (int i = 0; i < kStrategiesMax; ++i) ga.dehaze_idx[i] = e->dehaze_idx[i];
-        {
-            // row chunks: every chunk re-reads r - 1 warm-up rows, so as few as fill the machine ONCE
-            // (2 blocks per SM; all blocks do the same work, a second partial wave would only be a tail)
-            const int outw_min = 160 - e->max_radius + 1;
-            const int strips = (W + outw_min - 1) / outw_min;
-            const int per_chunk = ((strips + 7) / 8) * batch * e->n_dehaze;
-            int chunks = (148 * 2) / (per_chunk > 0 ? per_chunk : 1);
-            const int most = H / (3 * (e->max_radius > 0 ? e->max_radius : 1));
-            if (chunks > most) chunks = most;
-            if (chunks < 1) chunks = 1;
-            ga.rows_per_block = (H + chunks - 1) / chunks;
-        }
+        ga.rows_per_block = 0;                                // chosen by launch_guided (strip and chunk geometry live there)
         ga.gd_plane = e->at<uint2>(L.gf_gray);
         ga.eps_safe = e->eps_safe;
         ga.frames = frames; ga.cast = sa.cast; ga.light = qa.light;

@@ -51,7 +51,7 @@ class Engine:
             need = lib.uwie_workspace_bytes(C.byref(plib), arr, len(pst), self.max_batch, self.H, self.W)
             if need == 0:
                 _lib.check(_lib.ERR_ARG)
-            self.workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
+            self.workspace = _lib.scratch(need, self.device)       # poisoned / guarded under the test hooks
             h = C.c_void_p()
             _lib.check(lib.uwie_engine_create(C.byref(h), C.byref(plib), arr, len(pst), self.max_batch,
                                               self.H, self.W, C.c_void_p(self.workspace.data_ptr()), need))

@@ -41,7 +41,7 @@ def extract_all_features_batch(img, device="cuda:0") -> torch.Tensor:
     need = lib.uwie_features79_workspace_bytes(B, H, W)
     if need == 0:
         _lib.check(_lib.ERR_ARG)
-    ws = torch.empty(need, dtype=torch.uint8, device=frames.device)
+    ws = _lib.scratch(need, frames.device)
     feat = torch.empty((B, _lib.FEATURES), dtype=torch.float64, device=frames.device)
     stream = torch.cuda.current_stream(frames.device)
     with torch.cuda.device(frames.device):

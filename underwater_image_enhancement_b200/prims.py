@@ -38,7 +38,7 @@ def _p(t):
 
 
 def _ws(nbytes, dev):
-    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+    return _lib.scratch(nbytes, dev)
 
 
 def _float_image(img, device=None):
@@ -205,7 +205,7 @@ def scale_clip(img, scale3):
 def channel_means(img):
     t = _float_image(img)
     H, W, _ = t.shape
-    ws = _ws(512, t.device)
+    ws = _ws(4096, t.device)
     out = torch.empty(3, dtype=torch.float64, device=t.device)
     with torch.cuda.device(t.device):
         _lib.check(_lib.load().uwie_prim_channel_means(_p(t), _DT[t.dtype], H, W, _p(out), _p(ws), ws.numel(), _stream(t)))

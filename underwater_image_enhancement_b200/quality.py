@@ -33,7 +33,7 @@ def quality_scores_batch(img, weights=None, device="cuda:0") -> torch.Tensor:
     w = DEFAULT_WEIGHTS if weights is None else weights
     warr = (C.c_double * 8)(*[float(w.get(k, 0)) for k in QA_KEYS])                      # QA:284 weights.get(k, 0)
     need = lib.uwie_quality_workspace_bytes(B, H, W)
-    ws = torch.empty(need, dtype=torch.uint8, device=t.device)
+    ws = _lib.scratch(need, t.device)
     scores = torch.empty((B, _lib.SCORE_COLS), dtype=torch.float64, device=t.device)
     stream = torch.cuda.current_stream(t.device)
     with torch.cuda.device(t.device):

@@ -20,7 +20,7 @@ def _stream(dev):
 
 def _workspace(batch, dev):
     need = _lib.load().uwie_vgg_workspace_bytes(int(batch))
-    return torch.empty(need, dtype=torch.uint8, device=dev), need
+    return _lib.scratch(need, dev), need
 
 
 def _floats(x, batch, name):
