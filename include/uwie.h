@@ -306,7 +306,9 @@ int uwie_prim_channel_means(const void* img_dev, int dtype, int height, int widt
 /* ---------------------------------------------------------------------------------------------
  * Self-test of the guided filter's branch-free float64 division and reciprocal (k_arith.cuh) against the
  * compiler's IEEE-754 routines: `count` seeded operand pairs in the ranges the kernels guarantee
- * (divisor in [1e-9, 2], dividend 0 or |x| in [1e-18, 2]; reciprocal of t in [0.1, 1]).
+ * (divisor in [1e-9, 2], dividend 0 or |x| in [1e-18, 2]; reciprocal of t in [0.1, 1]), and of the percentile stretch's
+ * invariant-divisor division x / den = RN(q + (x - q * den) * r), r = RN(1 / den) (float32 and float64; den in [guard, 1 + guard],
+ * dividend 0 or 2^-30 <= |x| <= 1).
  * *mismatches_host receives the number of results whose bits differ (must be 0).  Synchronous.
  * ------------------------------------------------------------------------------------------- */
 int uwie_selftest_division(unsigned long long count, unsigned long long seed, unsigned long long* mismatches_host);

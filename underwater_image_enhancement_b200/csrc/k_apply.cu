@@ -65,11 +65,14 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
     for (int i = threadIdx.x; i < 768; i += NT) (&s_preq[0][0])[i] = (&st.preq[0][0])[i];
     const bool dehaze = rc.dehaze != 0;
     const int n_pre = rc.n_pre;
-    T lo[kMaxStretch][3], den[kMaxStretch][3];
+    T lo[kMaxStretch][3], den[kMaxStretch][3], rden[kMaxStretch][3];
 #pragma unroll
     for (int i = 0; i < kMaxStretch; ++i)
 #pragma unroll
-        for (int c = 0; c < 3; ++c) { lo[i][c] = (T)st.st_lo[i][c]; den[i][c] = (T)st.st_den[i][c]; }
+        for (int c = 0; c < 3; ++c) {
+            lo[i][c] = (T)st.st_lo[i][c]; den[i][c] = (T)st.st_den[i][c];
+            rden[i][c] = (i < n_pre && dehaze) ? InvDiv<T>::rcp(den[i][c]) : (T)0;   // unused slots hold garbage tables
+        }
     __syncthreads();
     unsigned* h = sh[threadIdx.x >> 5];
     const size_t npix = (size_t)a.H * a.W;
@@ -80,12 +83,12 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
     };
     auto count_floats = [&](T v0, T v1, T v2) {
         if (n_pre > 0) {
-            v0 = stretch_apply<T>(v0, lo[0][0], den[0][0]); v1 = stretch_apply<T>(v1, lo[0][1], den[0][1]);
-            v2 = stretch_apply<T>(v2, lo[0][2], den[0][2]);
+            v0 = stretch_apply_inv<T>(v0, lo[0][0], den[0][0], rden[0][0]); v1 = stretch_apply_inv<T>(v1, lo[0][1], den[0][1], rden[0][1]);
+            v2 = stretch_apply_inv<T>(v2, lo[0][2], den[0][2], rden[0][2]);
         }
         if (n_pre > 1) {
-            v0 = stretch_apply<T>(v0, lo[1][0], den[1][0]); v1 = stretch_apply<T>(v1, lo[1][1], den[1][1]);
-            v2 = stretch_apply<T>(v2, lo[1][2], den[1][2]);
+            v0 = stretch_apply_inv<T>(v0, lo[1][0], den[1][0], rden[1][0]); v1 = stretch_apply_inv<T>(v1, lo[1][1], den[1][1], rden[1][1]);
+            v2 = stretch_apply_inv<T>(v2, lo[1][2], den[1][2], rden[1][2]);
         }
         atomicAdd(&h[lab_L_only(s_gamma, s_cbrt, quantise<T>(v0), quantise<T>(v1), quantise<T>(v2))], 1u);
     };
@@ -239,11 +242,14 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
     }
     constexpr bool clahe = CLAHE, dehaze = DEHAZE;
     const int n_pre = rc.n_pre;
-    T lo[kMaxStretch][3], den[kMaxStretch][3];
+    T lo[kMaxStretch][3], den[kMaxStretch][3], rden[kMaxStretch][3];
 #pragma unroll
     for (int i = 0; i < kMaxStretch; ++i)
 #pragma unroll
-        for (int c = 0; c < 3; ++c) { lo[i][c] = (T)st.st_lo[i][c]; den[i][c] = (T)st.st_den[i][c]; }
+        for (int c = 0; c < 3; ++c) {
+            lo[i][c] = (T)st.st_lo[i][c]; den[i][c] = (T)st.st_den[i][c];
+            rden[i][c] = (i < n_pre && dehaze) ? InvDiv<T>::rcp(den[i][c]) : (T)0;   // unused slots hold garbage tables
+        }
     __syncthreads();
 
     TileGeo geo = {1, 1};
@@ -267,12 +273,12 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
     static_assert(kMaxStretch == 2, "pre_stretch is written out for two stretches");
     auto pre_stretch = [&](T& v0, T& v1, T& v2) {          // static indices keep lo / den in registers
         if (n_pre > 0) {
-            v0 = stretch_apply<T>(v0, lo[0][0], den[0][0]); v1 = stretch_apply<T>(v1, lo[0][1], den[0][1]);
-            v2 = stretch_apply<T>(v2, lo[0][2], den[0][2]);
+            v0 = stretch_apply_inv<T>(v0, lo[0][0], den[0][0], rden[0][0]); v1 = stretch_apply_inv<T>(v1, lo[0][1], den[0][1], rden[0][1]);
+            v2 = stretch_apply_inv<T>(v2, lo[0][2], den[0][2], rden[0][2]);
         }
         if (n_pre > 1) {
-            v0 = stretch_apply<T>(v0, lo[1][0], den[1][0]); v1 = stretch_apply<T>(v1, lo[1][1], den[1][1]);
-            v2 = stretch_apply<T>(v2, lo[1][2], den[1][2]);
+            v0 = stretch_apply_inv<T>(v0, lo[1][0], den[1][0], rden[1][0]); v1 = stretch_apply_inv<T>(v1, lo[1][1], den[1][1], rden[1][1]);
+            v2 = stretch_apply_inv<T>(v2, lo[1][2], den[1][2], rden[1][2]);
         }
     };
     // one pixel: bytes (no-dehaze) or floats (dehaze) in -> float value f and byte q per channel out.

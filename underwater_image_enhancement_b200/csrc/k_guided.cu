@@ -390,6 +390,20 @@ __global__ void selftest_div_kernel(unsigned long long count, unsigned long long
         if (__double_as_longlong(div_rn_normal(x, y)) != __double_as_longlong(__ddiv_rn(x, y))) ++mine;
         if (__double_as_longlong(div_rn_normal(x, tt)) != __double_as_longlong(__ddiv_rn(x, tt))) ++mine;
         if (__double_as_longlong(rcp_rn_normal(tt)) != __double_as_longlong(__drcp_rn(tt))) ++mine;
+        // invariant-divisor stretch division (k_arith.cuh: InvDiv): divisor in [guard, 1 + guard], dividend 0 or 2^-30 <= |x| <= 1
+        {
+            const unsigned long long h3 = mix64(seed + 3 * i + 0x5bd1e995ull), h4 = mix64(h3);
+            const double d64 = 1e-10 + rand_mag(h3, -33, 0);                     // [1e-10 + 1.2e-10, 1 + 1e-10)
+            double x64 = rand_mag(h4, -60, 0);
+            if (h4 & 1) x64 = -x64;
+            if ((h4 & 0xfe) == 0) x64 = 0.0;
+            if (__double_as_longlong(InvDiv<double>::div(x64, d64, InvDiv<double>::rcp(d64))) != __double_as_longlong(__ddiv_rn(x64, d64))) ++mine;
+            const float d32 = __fadd_rn((float)rand_mag(h4 ^ h3, -20, 0), 1e-6f);  // [1e-6 + 9.5e-7, 1 + 1e-6)
+            float x32 = (float)rand_mag(h3 ^ (h4 >> 7), -30, 0);
+            if (h3 & 1) x32 = -x32;
+            if ((h3 & 0xfe) == 0) x32 = 0.f;
+            if (__float_as_uint(InvDiv<float>::div(x32, d32, InvDiv<float>::rcp(d32))) != __float_as_uint(__fdiv_rn(x32, d32))) ++mine;
+        }
     }
     if (mine) atomicAdd(bad, mine);
 }

@@ -238,7 +238,9 @@ int init_engine_shape(uwie_engine* e, const uwie_library* lib, const uwie_strate
         }
     }
     const size_t N = (size_t)H * W;
-    e->pix_per_block = 8192;     // multiple of 4: apply_kernel moves 4-pixel groups as words
+    // multiple of 4: apply_kernel moves 4-pixel groups as words.  32768 (was 8192): the block prologue (13 KB of colour and
+    // strategy tables into shared memory) was 12 % of apply_kernel's stall samples with 32 pixels per thread
+    e->pix_per_block = 32768;
     e->final_blocks = (int)((N + e->pix_per_block - 1) / e->pix_per_block);
     // quadtree: upper bound of the quadrant size per level (ceil halves), enhancement_strategies.py:104-119
     e->quad_dims.clear();
