@@ -11,7 +11,8 @@ from underwater_image_enhancement_b200 import ops  # noqa: F401  (registers the 
 from underwater_image_enhancement_b200.synth import synth_image
 
 OPS = ("enhance_score_p6", "enhance_score_p5", "quality_scores", "features79", "vgg_enhance", "vgg_features",
-       "vgg_preprocess")
+       "vgg_preprocess", "clahe_lab", "equalize_hist", "transmission_head", "atmospheric_light", "transmission", "recover",
+       "percentile_stretch", "gamma")
 
 
 def test_operators_are_registered_for_cuda_only():
@@ -60,3 +61,28 @@ def test_other_operators_match_oracle():
     assert np.array_equal(enh, o.vgg_enhance(nchw.cpu().numpy(), [5.0], [95.0], [0.6], None))
     assert np.allclose(torch.ops.uwie.vgg_features(frames)[0].cpu().numpy(), o.vgg_features(frame), rtol=1e-5, atol=1e-7)
     assert np.array_equal(torch.ops.uwie.vgg_preprocess(frames, 224)[0].cpu().numpy(), o.vgg_preprocess(frame))
+
+
+@pytest.mark.gpu
+def test_primitive_operators_match_cv2_and_oracle():
+    import cv2
+    frame = synth_image(42, 96, 128)
+    L = torch.from_numpy(np.ascontiguousarray(cv2.cvtColor(frame, cv2.COLOR_RGB2LAB)[:, :, 0])[None]).cuda()
+    got = torch.ops.uwie.clahe_lab(L, 2.0, 8, 8)[0].cpu().numpy()
+    assert np.array_equal(got, cv2.createCLAHE(clipLimit=2.0, tileGridSize=(8, 8)).apply(L[0].cpu().numpy()))
+    eq = torch.ops.uwie.equalize_hist(torch.from_numpy(frame[None]).cuda())[0].cpu().numpy()
+    assert np.array_equal(eq[:, :, 1], cv2.equalizeHist(np.ascontiguousarray(frame[:, :, 1])))
+    img = np.random.default_rng(3).random((96, 128, 3))
+    d = torch.from_numpy(img).cuda()
+    A = torch.ops.uwie.atmospheric_light(d)
+    assert np.array_equal(A.cpu().numpy(), o.quadtree_airlight(img, 1))
+    t = torch.ops.uwie.transmission(d, A, 0.5, 15, 1e-3, 1e-10, False)
+    plane = np.tile(A.cpu().numpy().reshape(1, 1, 3), (96, 128, 1))
+    assert np.abs(t.cpu().numpy() - o.es_transmission(img, plane, 0.5, 15)).max() < 1e-9
+    rec = torch.ops.uwie.recover(d, t, A, True)
+    st = torch.ops.uwie.percentile_stretch(rec, 10.0, 95.0, 1e-10)
+    assert np.array_equal(st.cpu().numpy(), o.percentile_stretch(rec.cpu().numpy(), 10, 95, 1e-10))
+    g = torch.ops.uwie.gamma(st, 1 / 1.2, True)
+    assert np.abs(g.cpu().numpy() - o.es_gamma(st.cpu().numpy(), 1.2)).max() < 1e-15
+    th = torch.ops.uwie.transmission_head(torch.from_numpy(frame[None]).cuda(), torch.tensor([[0.3, 0.6, 0.7]], device="cuda"), 0.5, 1e-6, True)
+    assert th.shape == (1, 96, 128) and th.dtype == torch.float32

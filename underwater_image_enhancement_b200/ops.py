@@ -13,6 +13,15 @@ current stream to the C ABI of libuwie_b200.so through ctypes.
     uwie::vgg_enhance(Tensor img, Tensor l_low, Tensor l_high, Tensor? omega, Tensor? gamma) -> Tensor   vgg_16_UIE.py:32-55
     uwie::vgg_features(Tensor frames) -> Tensor                                          vgg_16_UIE.py:435-466
     uwie::vgg_preprocess(Tensor frames, int size) -> Tensor                              use_trained_model.py:39-46
+Per-primitive operators (csrc/k_prims.cu; float images are [H,W,3] float32 / float64 and need not be byte-valued):
+    uwie::clahe_lab(Tensor planes, float clip_limit, int tiles_x, int tiles_y) -> Tensor     uint8 [B,H,W]      ES:302-303, SS:205-206
+    uwie::equalize_hist(Tensor frames) -> Tensor                                           uint8 [B,H,W,3]    ES:339-343
+    uwie::transmission_head(Tensor frames, Tensor light, float omega, float guard, bool clip) -> Tensor   uint8 -> float32 [B,H,W]  SS:170-174
+    uwie::atmospheric_light(Tensor img) -> Tensor                                          (3,)               ES:77-206, SS:48-165
+    uwie::transmission(Tensor img, Tensor light, float omega, int r, float eps, float guard, bool clip_t0) -> Tensor   float64 [H,W]  ES:209-234, SS:167-180
+    uwie::recover(Tensor img, Tensor t, Tensor light, bool f64_out) -> Tensor             ES:237-249, SS:182-188
+    uwie::percentile_stretch(Tensor img, float lo, float hi, float guard) -> Tensor        ES:252-273, SS:190-219
+    uwie::gamma(Tensor img, float exponent, bool clip) -> Tensor                           ES:276-285, SS:221-224
 """
 from __future__ import annotations
 
@@ -31,6 +40,15 @@ _LIB.define("features79(Tensor frames) -> Tensor")
 _LIB.define("vgg_enhance(Tensor img, Tensor l_low, Tensor l_high, Tensor? omega, Tensor? gamma) -> Tensor")
 _LIB.define("vgg_features(Tensor frames) -> Tensor")
 _LIB.define("vgg_preprocess(Tensor frames, int size) -> Tensor")
+
+_LIB.define("clahe_lab(Tensor planes, float clip_limit, int tiles_x, int tiles_y) -> Tensor")
+_LIB.define("equalize_hist(Tensor frames) -> Tensor")
+_LIB.define("transmission_head(Tensor frames, Tensor light, float omega, float guard, bool clip) -> Tensor")
+_LIB.define("atmospheric_light(Tensor img) -> Tensor")
+_LIB.define("transmission(Tensor img, Tensor light, float omega, int r, float eps, float guard, bool clip_t0) -> Tensor")
+_LIB.define("recover(Tensor img, Tensor t, Tensor light, bool f64_out) -> Tensor")
+_LIB.define("percentile_stretch(Tensor img, float lo, float hi, float guard) -> Tensor")
+_LIB.define("gamma(Tensor img, float exponent, bool clip) -> Tensor")
 
 _ENGINES: dict = {}
 _CHUNK = 16          # frames per engine call: fewer, fuller launches (bench.py --chunk)
@@ -112,6 +130,19 @@ def _vgg_preprocess(frames, size):
     return preprocess_for_vgg(frames, size, device=frames.device)
 
 
+def _prim(name):
+    from . import prims
+    return getattr(prims, name)
+
+
+_LIB.impl("clahe_lab", lambda planes, clip, tx, ty: _prim("clahe_lab")(planes, clip, (tx, ty)), "CUDA")
+_LIB.impl("equalize_hist", lambda frames: _prim("equalize_hist")(frames), "CUDA")
+_LIB.impl("transmission_head", lambda frames, light, omega, guard, clip: _prim("transmission_head_u8")(frames, light, omega, guard, clip), "CUDA")
+_LIB.impl("atmospheric_light", lambda img: _prim("atmospheric_light")(img), "CUDA")
+_LIB.impl("transmission", lambda img, light, omega, r, eps, guard, clip_t0: _prim("transmission")(img, light, omega, r, eps, guard, clip_t0), "CUDA")
+_LIB.impl("recover", lambda img, t, light, f64_out: _prim("recover")(img, t, light, torch.float64 if f64_out else torch.float32), "CUDA")
+_LIB.impl("percentile_stretch", lambda img, lo, hi, guard: _prim("percentile_stretch")(img, lo, hi, guard), "CUDA")
+_LIB.impl("gamma", lambda img, exponent, clip: _prim("gamma")(img, exponent, clip), "CUDA")
 _LIB.impl("enhance_score_p6", _p6, "CUDA")
 _LIB.impl("enhance_score_p5", _p5, "CUDA")
 _LIB.impl("quality_scores", _quality, "CUDA")
