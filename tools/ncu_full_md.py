@@ -7,7 +7,8 @@ import subprocess
 import sys
 
 rep, title = sys.argv[1], sys.argv[2]
-rows = list(csv.reader(subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout.splitlines()))
+raw = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(raw.splitlines()))
 h, units = rows[0], rows[1]
 col = {c: i for i, c in enumerate(h)}
 keys = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
