@@ -287,3 +287,19 @@ def test_graph_replay_is_the_same_computation(cuda_device):
     side.synchronize()
     assert eng.graph_replays >= 2 and eng.last_launches > 0
     eng.close()
+
+
+@pytest.mark.parametrize("h,w", [(2, 2), (1, 40), (9, 11), (16, 16), (8, 64), (24, 40), (3, 1000), (700, 5)])
+@pytest.mark.parametrize("library", ["six", "es"])
+def test_tiny_and_ragged_frames(cuda_device, library, h, w):
+    """Frames smaller than a guided-filter window, a CLAHE tile grid or a Canny tile, one-pixel-wide / one-row frames
+    (the quadtree does not descend at all): whatever the reference computes (cv2 reflects borders as often as needed and
+    pads CLAHE tiles), the device computes too."""
+    frame = np.ascontiguousarray(synth_image(3, max(h, 2), max(w, 2))[:h, :w])
+    ref = o.p6_frame(frame) if library == "six" else o.p5_frame(frame)
+    res = _run(library, frame[None])
+    assert np.array_equal(res["light"][0], ref["light"])
+    d = np.abs(res["out"][0].astype(np.int16) - ref["out"].astype(np.int16))
+    assert d.max() <= PIXEL_ATOL, d.max()
+    assert _rel(res["scores"][0], ref["scores"]).max() < SCORE_RTOL
+    assert int(res["best"][0]) == ref["best"]
