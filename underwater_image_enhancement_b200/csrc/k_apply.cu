@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
         } else {
             T v0 = fr, v1 = fg, v2 = fb;
             pre_stretch(v0, v1, v2);
-            f[0] = apply_gamma<T>(v0, rc); f[1] = apply_gamma<T>(v1, rc); f[2] = apply_gamma<T>(v2, rc);
+            f[0] = apply_gamma_bytes<T>(v0, rc); f[1] = apply_gamma_bytes<T>(v1, rc); f[2] = apply_gamma_bytes<T>(v2, rc);
             q[0] = quantise<T>(f[0]); q[1] = quantise<T>(f[1]); q[2] = quantise<T>(f[2]);
         }
         return true;
