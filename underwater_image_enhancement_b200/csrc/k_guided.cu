@@ -21,6 +21,8 @@
 // The kernels are bound by instruction issue and load latency, not by HBM: rows are addressed as a
 // warp-uniform row pointer plus a 32-bit column, records are fetched whole (64 / 128 bits), and the
 // {a, b} pairs leave straight from the registers that computed them.
+#include <cstdlib>
+
 #include "k_arith.cuh"
 #include "k_kernels.h"
 
@@ -437,9 +439,13 @@ int launch_guided(const GuidedArgs& a0, int max_radius, cudaStream_t st) {
     const int nt = 32 * ((strips + bx - 1) / bx);
     // row chunks: every chunk re-reads r - 1 warm-up rows, so as few as fill the machine ONCE
     // (all blocks do the same work, a second partial wave would only be a tail)
+    // UWIE_GF_BLOCKS_PER_SM=1 (experiment): one block per SM, enforced by padding the dynamic shared memory, so
+    // that the kernels of OTHER lanes can share the SM with these latency-bound ones instead of queueing behind them
+    static const int per_sm = [] { const char* v = std::getenv("UWIE_GF_BLOCKS_PER_SM"); return (v && v[0] == '1') ? 1 : GBLOCKS_PER_SM; }();
+    const size_t pad = per_sm == 1 ? 120 * 1024 : 0;
     {
         const int per_chunk = bx * inst;
-        int chunks = (148 * GBLOCKS_PER_SM) / (per_chunk > 0 ? per_chunk : 1);
+        int chunks = (148 * per_sm) / (per_chunk > 0 ? per_chunk : 1);
         const int most = a.H / (3 * (max_radius > 0 ? max_radius : 1));
         if (chunks > most) chunks = most;
         if (chunks < 1) chunks = 1;
@@ -447,20 +453,25 @@ int launch_guided(const GuidedArgs& a0, int max_radius, cudaStream_t st) {
     }
     const int chunks = (a.H + a.rows_per_block - 1) / a.rows_per_block;
     dim3 grid(bx, chunks, inst);
-    if (a.lib.clip_t0) {
-        if (a.eps_safe) gf_ab_kernel<true, true><<<grid, nt, 0, st>>>(a);
-        else gf_ab_kernel<true, false><<<grid, nt, 0, st>>>(a);
-    } else {
-        if (a.eps_safe) gf_ab_kernel<false, true><<<grid, nt, 0, st>>>(a);
-        else gf_ab_kernel<false, false><<<grid, nt, 0, st>>>(a);
-    }
     static const bool optin = [] {
-        return cudaFuncSetAttribute(gf_recover_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RecoverShared)) == cudaSuccess &&
-               cudaFuncSetAttribute(gf_recover_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RecoverShared)) == cudaSuccess;
+        const int most = 128 * 1024, most_r = (int)sizeof(RecoverShared) + 120 * 1024;   // + static: below the 227 KB of an SM
+        return cudaFuncSetAttribute(gf_recover_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, most_r) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_recover_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, most_r) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess;
     }();
     (void)optin;                                        // a failure shows up as a launch error below
-    if (a.lib.f64) gf_recover_kernel<double><<<grid, nt, sizeof(RecoverShared), st>>>(a);
-    else gf_recover_kernel<float><<<grid, nt, sizeof(RecoverShared), st>>>(a);
+    if (a.lib.clip_t0) {
+        if (a.eps_safe) gf_ab_kernel<true, true><<<grid, nt, pad, st>>>(a);
+        else gf_ab_kernel<true, false><<<grid, nt, pad, st>>>(a);
+    } else {
+        if (a.eps_safe) gf_ab_kernel<false, true><<<grid, nt, pad, st>>>(a);
+        else gf_ab_kernel<false, false><<<grid, nt, pad, st>>>(a);
+    }
+    if (a.lib.f64) gf_recover_kernel<double><<<grid, nt, sizeof(RecoverShared) + pad, st>>>(a);
+    else gf_recover_kernel<float><<<grid, nt, sizeof(RecoverShared) + pad, st>>>(a);
     return 3;
 }
 
