@@ -4,30 +4,28 @@ import numpy as np
 import _bootstrap  # noqa: F401
 from underwater_image_enhancement_b200.quality import QualityAssessment  # noqa: F401
 
+_COLUMNS = (("影像", None), ("總分", None), ("對比度", "contrast"), ("清晰度", "sharpness"), ("熵", "entropy"), ("飽和度", "saturation"))
 
-def test_quality_assessment():
-    """quality_assessment.py:289-318."""
-    print("測試品質評估...")
-    test_images = {
-        'Random': np.random.rand(256, 256, 3),
-        'Low Contrast': np.ones((256, 256, 3)) * 0.5,
-        'High Contrast': np.random.choice([0.0, 1.0], size=(256, 256, 3)),
-        'Dark': np.random.rand(256, 256, 3) * 0.3,
-        'Bright': 0.7 + np.random.rand(256, 256, 3) * 0.3
-    }
-    print("\n評估結果:")
-    print("-" * 80)
-    print(f"{'影像':<15} {'總分':<10} {'對比度':<10} {'清晰度':<10} {'熵':<10} {'飽和度':<10}")
-    print("-" * 80)
-    out = {}
-    for name, img in test_images.items():
-        total_score, scores = QualityAssessment.comprehensive_assessment(img)
-        out[name] = (total_score, scores)
-        print(f"{name:<15} {total_score:>6.2f}    {scores['contrast']:>6.2f}    {scores['sharpness']:>6.2f}    "
-              f"{scores['entropy']:>6.2f}    {scores['saturation']:>6.2f}")
-    print("-" * 80)
-    print("✓ 品質評估測試完成")
-    return out
+
+def test_quality_assessment(size=256, seed=None):
+    """Module self-test with the five synthetic images of quality_assessment.py:289-318 (random, flat, binary, dark,
+    bright); prints the same table and returns {name: (total, sub-scores)}."""
+    rng = np.random.default_rng(seed)
+    shape = (size, size, 3)
+    cases = {"Random": rng.random(shape), "Low Contrast": np.full(shape, 0.5),
+             "High Contrast": rng.integers(0, 2, shape).astype(np.float64),
+             "Dark": 0.3 * rng.random(shape), "Bright": 0.7 + 0.3 * rng.random(shape)}
+    rule = "-" * 80
+    print("測試品質評估...\n\n評估結果:\n" + rule)
+    print(f"{_COLUMNS[0][0]:<15} " + " ".join(f"{title:<10}" for title, _ in _COLUMNS[1:]) + "\n" + rule)
+    results = {}
+    for label, image in cases.items():
+        results[label] = QualityAssessment.comprehensive_assessment(image)
+        total, sub = results[label]
+        cells = [total] + [sub[key] for _, key in _COLUMNS[2:]]
+        print(f"{label:<15} " + "    ".join(f"{v:>6.2f}" for v in cells))
+    print(rule + "\n✓ 品質評估測試完成")
+    return results
 
 
 if __name__ == '__main__':

@@ -1,24 +1,25 @@
 """Drop-in for the reference's use_trained_model.py (use_trained_model.py:13-295): EnhancementPredictor with the
 reference's constructor and methods, batched on the B200; the network itself is the reference's own
 ImprovedVGGParameterNet (vgg_16_UIE.py stays where it is, stock PyTorch)."""
-import argparse
-from pathlib import Path
-
 import _bootstrap  # noqa: F401
 from underwater_image_enhancement_b200.predictor import EnhancementPredictor  # noqa: F401
 
-if __name__ == '__main__':
-    parser = argparse.ArgumentParser(description='使用 vgg-16_UIE 模型進行影像增強')
-    parser.add_argument('--input', type=str, required=True, help='輸入影像或資料夾')
-    parser.add_argument('--output', type=str, required=True, help='輸出檔案或資料夾')
-    parser.add_argument('--model', type=str, required=True, help='模型檔案（checkpoint）')
-    parser.add_argument('--device', type=str, default='cuda', choices=['cuda', 'cpu'])
-    args = parser.parse_args()
-    predictor = EnhancementPredictor(model_path=args.model, device=args.device)
-    input_path = Path(args.input)
-    if input_path.is_file():
-        predictor.process_single_image(args.input, args.output)
-    elif input_path.is_dir():
-        predictor.process_folder(args.input, args.output)
-    else:
+
+def _cli():
+    """Same flags as use_trained_model.py:278-295 (--input file or folder, --output, --model, --device)."""
+    import argparse
+    import os
+    p = argparse.ArgumentParser(description="vgg-16_UIE 模型影像增強 (B200)")
+    for flag, text in (("--input", "輸入影像或資料夾"), ("--output", "輸出檔案或資料夾"), ("--model", "模型檔案（checkpoint）")):
+        p.add_argument(flag, required=True, help=text)
+    p.add_argument("--device", default="cuda", choices=["cuda", "cpu"])
+    a = p.parse_args()
+    if not os.path.exists(a.input):
         raise ValueError("輸入路徑不存在或不是檔案/資料夾")
+    predictor = EnhancementPredictor(model_path=a.model, device=a.device)
+    run = predictor.process_folder if os.path.isdir(a.input) else predictor.process_single_image
+    run(a.input, a.output)
+
+
+if __name__ == '__main__':
+    _cli()
