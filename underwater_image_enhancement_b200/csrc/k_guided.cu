@@ -41,6 +41,10 @@ constexpr int GNT = 32 * GWARPS;
 constexpr int GBLOCKS_PER_SM = GC <= 3 ? 3 : 2;
 
 // ------------------------------------------------------------------ gray + dark channel records
+// (Round 2 tried this kernel with TMA-staged tiles like uwie_prim_transmission_head_u8 - cp.async.bulk + mbarrier, persistent
+// one-wave blocks or short-lived two-tile blocks: 2 x faster alone, 1.7 -> 1.0 ms per 256-frame step, but the four-lane
+// step lost 4.5 %, 2 760 -> 2 640 frames/s, with either shape and with one polling thread: small blocks of plain loads
+// share the SMs with the other lanes' kernels better than 24-41 KB blocks waiting on a barrier.  Kept as it was.)
 __global__ void __launch_bounds__(256) gf_prep_kernel(GuidedArgs a) {
     const int b = blockIdx.y;
     __shared__ float sdiv[3][256];      // img / (A + guard), float32            SS:170, ES:221

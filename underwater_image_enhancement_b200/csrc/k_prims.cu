@@ -92,7 +92,10 @@ __global__ void __launch_bounds__(TH_NT) thead_kernel(THeadArgs a) {
     for (unsigned k = blockIdx.x; k < ntiles; k += gridDim.x) {
         const unsigned np = tile_pix(k);
         if (bulk_ok(k)) {
-            tma::mbar_wait(&full[s], (phases >> s) & 1u);
+            // one thread polls the barrier, the block waits at bar.sync: 256 polling threads would take issue slots from
+            // the co-resident kernels of other streams (measured: -4.5 % on the four-lane step)
+            if (t == 0) tma::mbar_wait(&full[s], (phases >> s) & 1u);
+            __syncthreads();
             phases ^= 1u << s;
         } else {                                    // unaligned frame or ragged last tile: plain loads
             const uint8_t* src = f + (size_t)k * TH_PIX * 3;
