@@ -201,6 +201,46 @@ def main(cpu=None, out_path=None):
     cpu_s = cpu_time(cpu, "quality_scores", fr_np[0].astype(np.float32) / 255.0)
     emit("quality_scores", "quality_assessment.py:215-286", h, w, batch, 3, ms, "u8", cpu_s)
 
+    # ---- (f-1) the file loop: PNG files in -> six PNG files out per frame, through the pinned double-buffered reader / writer
+    try:
+        import shutil
+        import tempfile
+        import cv2
+        from underwater_image_enhancement_b200 import compat as _compat
+        tmp = tempfile.mkdtemp(prefix="uwie_io_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+        src, dst = os.path.join(tmp, "in"), os.path.join(tmp, "out")
+        os.makedirs(src)
+        nfiles = 48
+        for i in range(nfiles):
+            cv2.imwrite(os.path.join(src, f"f{i:03d}.png"), cv2.cvtColor(fr_np[i % len(fr_np)], cv2.COLOR_RGB2BGR))
+        workers = max(2, min(32, (os.cpu_count() or 4)))
+        _compat.process_all_images_all_strategies(src, dst, batch=8, workers=workers, write_csv=False)      # warm-up (engine, pools)
+        shutil.rmtree(dst)
+        t0 = time.perf_counter()
+        log = _compat.process_all_images_all_strategies(src, dst, batch=8, workers=workers)
+        dt = time.perf_counter() - t0
+        t1 = time.perf_counter()
+        for i in range(8):
+            cv2.imread(os.path.join(src, f"f{i:03d}.png"))
+        dec = (time.perf_counter() - t1) / 8
+        t1 = time.perf_counter()
+        for i in range(8):
+            cv2.imwrite(os.path.join(tmp, f"e{i}.png"), fr_np[i % len(fr_np)])
+        enc = (time.perf_counter() - t1) / 8
+        ok = sum(r["status"] == "success" for r in log)
+        rec = {"entry": "file_loop_six", "reference": "six_stadigy.py:326-470 (process_all_images_all_strategies)", "size": f"{w}x{h}",
+               "files": nfiles, "outputs_written": ok, "seconds": round(dt, 3), "frames_per_s": round(nfiles / dt, 1),
+               "workers": workers, "png_decode_ms_one_thread": round(dec * 1e3, 1), "png_encode_ms_one_thread": round(enc * 1e3, 1),
+               "note": "PNG files on tmpfs in, 6 PNG files + processing_log.csv out; decode / encode on worker threads (cv2 releases the "
+                       "GIL), pinned double-buffered slots around uwie_enhance_score_host; the ceiling is the host's PNG codec: "
+                       "workers / (decode + 6 x encode) frames/s"}
+        lines.append(rec)
+        print(json.dumps(rec), flush=True)
+        _compat.close_engines()
+        shutil.rmtree(tmp, ignore_errors=True)
+    except Exception as e:                                                          # noqa: BLE001
+        print(json.dumps({"entry": "file_loop_six", "unavailable": f"{type(e).__name__}: {e}"}), flush=True)
+
     if out_path:
         with open(out_path, "w") as f:
             for rec in lines:
