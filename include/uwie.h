@@ -254,6 +254,19 @@ int uwie_prim_clahe_lab(const uint8_t* plane_dev, int batch, int height, int wid
 int uwie_prim_equalize_hist(const uint8_t* frames_dev, int batch, int height, int width, uint8_t* out_dev,
                             void* workspace_dev, size_t workspace_bytes, void* stream);
 
+/* Allocation-free variant of uwie_prim_equalize_hist.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  Same arguments and same result as uwie_prim_equalize_hist, minus
+ * the workspace: the histograms and byte tables live in a static device array inside the library
+ * (UWIE_EQ_STATIC_MAX_BATCH x 3840 bytes = 240 KB on every GPU that loads the library, until the process exits).
+ * batch > UWIE_EQ_STATIC_MAX_BATCH returns UWIE_ERR_ARG (split the batch).  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine); the device of `stream` must be current.  All calls on a device share the
+ * array: calls whose GPU work can overlap (different streams without ordering) race and must be serialised by the
+ * caller; calls on one stream are safe back to back. */
+#define UWIE_EQ_STATIC_MAX_BATCH 64
+int uwie_prim_equalize_hist_static(const uint8_t* frames_dev, int batch, int height, int width, uint8_t* out_dev,
+                                   void* stream);
+
 /* (img * 255).astype(uint8) of `count` float values (ES:298, SS:204, QA:25). */
 int uwie_prim_quantise(const void* img_dev, int dtype, size_t count, uint8_t* out_dev, void* stream);
 

@@ -22,7 +22,7 @@ EXPORTS = ("uwie_version", "uwie_last_error", "uwie_preset", "uwie_workspace_byt
            "uwie_vgg_preprocess_u8", "uwie_vgg_preprocess_f32", "uwie_features79_workspace_bytes",
            "uwie_features79", "uwie_quality_workspace_bytes", "uwie_quality_scores", "uwie_selftest_division",
            "uwie_prim_transmission_head_u8", "uwie_prim_clahe_lab_workspace_bytes", "uwie_prim_clahe_lab",
-           "uwie_prim_equalize_hist", "uwie_prim_quantise", "uwie_prim_atmospheric_light_workspace_bytes",
+           "uwie_prim_equalize_hist", "uwie_prim_equalize_hist_static", "uwie_prim_quantise", "uwie_prim_atmospheric_light_workspace_bytes",
            "uwie_prim_atmospheric_light", "uwie_prim_guided_filter_workspace_bytes", "uwie_prim_guided_filter",
            "uwie_prim_transmission_workspace_bytes", "uwie_prim_transmission", "uwie_prim_recover",
            "uwie_prim_percentile_stretch_workspace_bytes", "uwie_prim_percentile_stretch", "uwie_prim_gamma",
@@ -134,6 +134,7 @@ def load() -> C.CDLL:
         "uwie_prim_clahe_lab_workspace_bytes": ([ci, ci, ci], cz),
         "uwie_prim_clahe_lab": ([vp, ci, ci, ci, cd, ci, ci, vp, vp, cz, vp], ci),
         "uwie_prim_equalize_hist": ([vp, ci, ci, ci, vp, vp, cz, vp], ci),
+        "uwie_prim_equalize_hist_static": ([vp, ci, ci, ci, vp, vp], ci),
         "uwie_prim_quantise": ([vp, ci, cz, vp, vp], ci),
         "uwie_prim_atmospheric_light_workspace_bytes": ([ci, ci], cz),
         "uwie_prim_atmospheric_light": ([vp, ci, ci, ci, vp, vp, cz, vp], ci),

@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "../../include/uwie.h"
@@ -1188,3 +1189,58 @@ int uwie_prim_channel_means(const void* img_dev, int dtype, int height, int widt
 }
 
 }  // extern "C"
+
+// =====================================================================================
+// Allocation-free variant of uwie_prim_equalize_hist (no counterpart in the reference; added for callers that
+// cannot allocate: graph capture, serving loops).  The channel histograms and the byte tables live in a
+// file-scope device array instead of a caller workspace: UWIE_EQ_STATIC_MAX_BATCH frames x 3840 bytes = 240 KB,
+// held by every GPU that loads the library until the process exits.
+// In host code `g_eq_scratch` is only a handle of the symbol, not a device address: its address on the CURRENT
+// device comes from cudaGetSymbolAddress, looked up once per device and cached; the kernels get that pointer.
+// All calls on one device share the array: the histogram part is cleared on `stream` before every use, and two
+// calls whose work overlaps on the GPU (different streams, no ordering) race on it.
+// =====================================================================================
+static __device__ __align__(256) unsigned char g_eq_scratch[(size_t)UWIE_EQ_STATIC_MAX_BATCH * 3840];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_eq_mutex;
+void* g_eq_addr[kMaxDevices] = {};          // device address of g_eq_scratch, per device ordinal
+
+int eq_scratch_address(void** out) {
+    int dev = -1;
+    PCU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return uwie_fail(UWIE_ERR_ARG, "equalize_hist_static: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_eq_mutex);
+    if (!g_eq_addr[dev]) {
+        void* p = nullptr;
+        PCU(cudaGetSymbolAddress(&p, g_eq_scratch));
+        if (!p) return uwie_fail(UWIE_ERR_CUDA, "equalize_hist_static: cudaGetSymbolAddress returned a null address");
+        g_eq_addr[dev] = p;
+    }
+    *out = g_eq_addr[dev];
+    return UWIE_OK;
+}
+}  // namespace
+
+extern "C" int uwie_prim_equalize_hist_static(const uint8_t* frames_dev, int batch, int height, int width, uint8_t* out_dev,
+                                              void* stream) {
+    if (!frames_dev || !out_dev || batch < 1 || height < 1 || width < 1)
+        return uwie_fail(UWIE_ERR_ARG, "equalize_hist_static: bad arguments");
+    if (batch > UWIE_EQ_STATIC_MAX_BATCH)
+        return uwie_fail(UWIE_ERR_ARG, "equalize_hist_static: batch " + std::to_string(batch) + " exceeds the static scratch's maximum of " +
+                                           std::to_string(UWIE_EQ_STATIC_MAX_BATCH) + " frames per call");
+    void* base = nullptr;
+    const int rc = eq_scratch_address(&base);
+    if (rc != UWIE_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned* hist = static_cast<unsigned*>(base);                              // [batch][3][256] counts
+    uint8_t* lut = reinterpret_cast<uint8_t*>(hist + (size_t)batch * 768);      // [batch][3][256] byte tables
+    PCU(cudaMemsetAsync(hist, 0, (size_t)batch * 768 * 4, st));                 // the array keeps the last call's counts
+    launch_frame_hist(frames_dev, batch, height, width, hist, st);
+    eq_lut_kernel<<<batch, 32, 0, st>>>(hist, (long long)height * width, lut);
+    const size_t npix = (size_t)height * width;
+    byte_map_kernel<<<dim3(grid_for(npix * 3, 256, 148 * 4), batch), 256, 0, st>>>(frames_dev, npix, lut, out_dev);
+    PCU(cudaGetLastError());
+    return UWIE_OK;
+}
