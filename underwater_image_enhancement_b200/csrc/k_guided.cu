@@ -33,7 +33,8 @@ namespace {
 // Columns per lane (odd: conflict-free 64-bit shared accesses).  Measured in round 2: 3 columns per lane (80 registers,
 // three blocks = 24 warps per SM, but 96 - r + 1 outputs of 96 columns instead of 160 - r + 1 of 160 and the per-row
 // shuffles / loop overhead spread over fewer pixels) is SLOWER than 5 (128 registers, 14 warps): 44.9 vs 32.1 ms per
-// 256-frame step.
+// 256-frame step.  Register budget at GC = 5, also measured in round 2 (per-kernel __maxnreg__): 96 registers (three 7-warp
+// blocks per SM, 40-104 bytes spilled) 55.8 ms; 144 registers (no spills, two blocks) 39.3 ms; 128 registers 32.1 ms - kept.
 constexpr int GC = 5;
 constexpr int GSPAN = 32 * GC;        // columns a warp carries, outputs = GSPAN - r + 1
 constexpr int GWARPS = 8;
