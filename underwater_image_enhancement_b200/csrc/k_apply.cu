@@ -203,8 +203,11 @@ __device__ __forceinline__ int clahe_interp(const uint8_t* luts, int tiles_x, fl
 }
 
 // ---------------------------------------------------------------- per-pixel tail of a strategy
-// FINAL = false: only the per-channel histograms of the CLAHE output (strategies with post-stretches)
-// FINAL = true : output bytes, gray plane, scoring accumulators
+// FINAL = false: the CLAHE output of strategies with post-stretches: its per-channel histograms (the post-stretch
+//                 percentiles come from them) and its bytes, left in the strategy's slot of `out`
+// FINAL = true : output bytes, gray plane, scoring accumulators.  A strategy that went through the FINAL = false pass
+//                continues from the bytes in `out` (in place) as a plain table pass: the Lab round trip and the tile
+//                interpolation run once per pixel, not twice.
 // A block owns pix_per_block consecutive pixels; a thread takes 4 consecutive pixels at a time so that
 // frame bytes, recovered floats, output bytes and gray bytes move as 32 / 128-bit words.  The colour
 // tables and the strategy's byte tables are staged in shared memory once per block.
@@ -220,7 +223,8 @@ template <class T> struct Vec4 { T v[4][3]; };
 // library), so a pixel runs straight-line code and a kernel carries only its own path.
 template <class T, bool FINAL, bool CLAHE, bool DEHAZE>
 __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
-    const int s = a.var_s[(CLAHE ? 2 : 0) + (DEHAZE ? 1 : 0)][blockIdx.y], b = blockIdx.z;
+    constexpr int variant = (CLAHE ? 2 : 0) + (DEHAZE ? 1 : 0);
+    const int s = FINAL ? a.fin_s[variant][blockIdx.y] : a.var_s[variant][blockIdx.y], b = blockIdx.z;
     const Recipe& rc = a.recipes[s];
     if (!FINAL && !(rc.clahe && rc.n_post > 0)) return;
     const StratTables& st = a.tables[(size_t)b * a.S + s];
@@ -261,12 +265,13 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
         inv_tw = __fdiv_rn(1.0f, (float)geo.tw);
         inv_th = __fdiv_rn(1.0f, (float)geo.th);
     }
-    const uint8_t* frame = a.frames + (size_t)b * npix * 3;
-    const T* rec = dehaze ? reinterpret_cast<const T*>(a.recovered) + (size_t)(b * a.n_dehaze + a.dehaze_slot[s]) * npix * 3 : nullptr;
-    uint8_t* out = FINAL ? a.out + bs * (size_t)npix * 3 : nullptr;
+    uint8_t* out = a.out + bs * (size_t)npix * 3;
     uint8_t* gray = FINAL ? a.gray + bs * (size_t)npix : nullptr;
-    const bool words_ok = (reinterpret_cast<uintptr_t>(frame) & 3) == 0 &&
-                          (!FINAL || (((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(gray)) & 3) == 0));
+    const bool in_place = FINAL && !CLAHE && !DEHAZE && a.from_out[s] != 0;      // block-uniform
+    const uint8_t* frame = in_place ? out : a.frames + (size_t)b * npix * 3;
+    const T* rec = dehaze ? reinterpret_cast<const T*>(a.recovered) + (size_t)(b * a.n_dehaze + a.dehaze_slot[s]) * npix * 3 : nullptr;
+    const bool words_ok = ((reinterpret_cast<uintptr_t>(frame) | reinterpret_cast<uintptr_t>(out)) & 3) == 0 &&
+                          (!FINAL || (reinterpret_cast<uintptr_t>(gray) & 3) == 0);
     double m_rg = 0, m_rg2 = 0, m_yb = 0, m_yb2 = 0;
     unsigned long long lum = 0;
 
@@ -282,7 +287,7 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
         }
     };
     // one pixel: bytes (no-dehaze) or floats (dehaze) in -> float value f and byte q per channel out.
-    // Returns false when the pixel only feeds the HIST pass.
+    // In the HIST pass q receives the CLAHE output bytes and f is not written.
     auto shade = [&](int r8, int g8, int b8, T fr, T fg, T fb, const ClaheRow& row, int x, T* f, int* q) -> bool {
         if (clahe) {
             int r, g, bl, L, A, Bc;
@@ -298,7 +303,8 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
             lab_to_rgb(sm.ct.lab_yf, sm.ct.gamma_out, L, A, Bc, k0, k1, k2);
             if (!FINAL) {
                 atomicAdd(&sh_a[0][k0], 1u); atomicAdd(&sh_a[1][k1], 1u); atomicAdd(&sh_a[2][k2], 1u);
-                return false;
+                q[0] = k0; q[1] = k1; q[2] = k2;
+                return true;
             }
             f[0] = s_postf[0][k0]; f[1] = s_postf[1][k1]; f[2] = s_postf[2][k2];
             q[0] = sm.postq[0][k0]; q[1] = sm.postq[1][k1]; q[2] = sm.postq[2][k2];
@@ -335,7 +341,8 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
         T d[12];
         if (!dehaze) {
             const uint32_t* w = reinterpret_cast<const uint32_t*>(frame + (size_t)p * 3);
-            w0 = __ldg(w); w1 = __ldg(w + 1); w2 = __ldg(w + 2);
+            if (in_place) { w0 = w[0]; w1 = w[1]; w2 = w[2]; }      // these bytes are overwritten below: no read-only path
+            else { w0 = __ldg(w); w1 = __ldg(w + 1); w2 = __ldg(w + 2); }
         } else if (sizeof(T) == 4 && (reinterpret_cast<uintptr_t>(rec + (size_t)p * 3) & 15) == 0) {
             const float4* qv = reinterpret_cast<const float4*>(rec + (size_t)p * 3);
             f0 = qv[0]; f1 = qv[1]; f2 = qv[2];
@@ -357,30 +364,30 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
         // pixel 0: bytes 0..2
         if (shade(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255, d[0], d[1], d[2], row, x, f, q)) {
             o0 = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16);
-            gw = (uint32_t)account(f, q);
+            if (FINAL) gw = (uint32_t)account(f, q);
         }
         if (++x == a.W) { x = 0; ++y; if (clahe) row = clahe_row(tiles_x, tiles_y, inv_th, y); }
         // pixel 1: bytes 3..5
         if (shade(w0 >> 24, w1 & 255, (w1 >> 8) & 255, d[3], d[4], d[5], row, x, f, q)) {
             o0 |= (uint32_t)q[0] << 24; o1 = (uint32_t)q[1] | ((uint32_t)q[2] << 8);
-            gw |= (uint32_t)account(f, q) << 8;
+            if (FINAL) gw |= (uint32_t)account(f, q) << 8;
         }
         if (++x == a.W) { x = 0; ++y; if (clahe) row = clahe_row(tiles_x, tiles_y, inv_th, y); }
         // pixel 2: bytes 6..8
         if (shade((w1 >> 16) & 255, w1 >> 24, w2 & 255, d[6], d[7], d[8], row, x, f, q)) {
             o1 |= ((uint32_t)q[0] << 16) | ((uint32_t)q[1] << 24); o2 = (uint32_t)q[2];
-            gw |= (uint32_t)account(f, q) << 16;
+            if (FINAL) gw |= (uint32_t)account(f, q) << 16;
         }
         if (++x == a.W) { x = 0; ++y; if (clahe) row = clahe_row(tiles_x, tiles_y, inv_th, y); }
         // pixel 3: bytes 9..11
         if (shade((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24, d[9], d[10], d[11], row, x, f, q)) {
             o2 |= ((uint32_t)q[0] << 8) | ((uint32_t)q[1] << 16) | ((uint32_t)q[2] << 24);
-            gw |= (uint32_t)account(f, q) << 24;
+            if (FINAL) gw |= (uint32_t)account(f, q) << 24;
         }
-        if (FINAL) {
+        {
             uint32_t* o = reinterpret_cast<uint32_t*>(out + (size_t)p * 3);
             o[0] = o0; o[1] = o1; o[2] = o2;
-            *reinterpret_cast<uint32_t*>(gray + p) = gw;
+            if (FINAL) *reinterpret_cast<uint32_t*>(gray + p) = gw;
         }
     }
     // what is left: the last 1-3 pixels of the frame, or everything when the buffers are not word-aligned
@@ -393,7 +400,7 @@ __global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
         const ClaheRow row = clahe ? clahe_row(tiles_x, tiles_y, inv_th, y) : ClaheRow{0, 0, 0.f, 0.f};
         if (shade(fp[0], fp[1], fp[2], d0, d1, d2, row, x, f, q)) {
             out[(size_t)p * 3] = (uint8_t)q[0]; out[(size_t)p * 3 + 1] = (uint8_t)q[1]; out[(size_t)p * 3 + 2] = (uint8_t)q[2];
-            gray[p] = (uint8_t)account(f, q);
+            if (FINAL) gray[p] = (uint8_t)account(f, q);
         }
     }
     __syncthreads();
@@ -436,8 +443,9 @@ template <class T, bool FINAL>
 int launch_apply_t(const ApplyArgs& a, cudaStream_t st) {
     int launches = 0;
     for (int v = FINAL ? 0 : 2; v < 4; ++v) {              // the histogram pass exists for CLAHE strategies only
-        if (a.var_n[v] == 0 || (!FINAL && a.var_hist[v] == 0)) continue;
-        dim3 grid(a.final_blocks, a.var_n[v], a.B);
+        const int n = FINAL ? a.fin_n[v] : a.var_n[v];
+        if (n == 0 || (!FINAL && a.var_hist[v] == 0)) continue;
+        dim3 grid(a.final_blocks, n, a.B);
         switch (v) {
             case 0: apply_kernel<T, FINAL, false, false><<<grid, NT, 0, st>>>(a); break;
             case 1: apply_kernel<T, FINAL, false, true><<<grid, NT, 0, st>>>(a); break;

@@ -48,6 +48,7 @@ struct DctArgs {
     const float* Ah;     // parity matrices of length H ([split][H/split][H/split])
     const float* Btw;    // transposed parity matrices of length W
     double* sums;        // [B][5]: total, low, mid, high, sum |z|
+    double* part;        // [B][blocks of step 2][5]: per-block sums, added in block order by dct_reduce_kernel
     int H, W, split_h, split_w;
 };
 
@@ -207,8 +208,18 @@ __global__ void __launch_bounds__(GNT, 2) dct_cols_kernel(DctArgs a) {
     if (threadIdx.x < 5) {
         double s = 0;
         for (int w = 0; w < GNT / 32; ++w) s += red[w][threadIdx.x];
-        atomicAdd(&a.sums[(size_t)b * 5 + threadIdx.x], s);
+        const size_t blk = (size_t)b * gridDim.x * gridDim.y + (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+        a.part[blk * 5 + threadIdx.x] = s;
     }
+}
+
+// the block sums of one frame in block order: the five results do not depend on how the blocks were scheduled
+__global__ void dct_reduce_kernel(const double* __restrict__ part, int nblk, double* __restrict__ sums) {
+    const int b = blockIdx.x;
+    if (threadIdx.x >= 5) return;
+    double s = 0;
+    for (int i = 0; i < nblk; ++i) s += part[((size_t)b * nblk + i) * 5 + threadIdx.x];
+    sums[(size_t)b * 5 + threadIdx.x] = s;
 }
 
 struct CacheEntry { float* A; float* Bt; int split; };
@@ -239,17 +250,26 @@ int matrices_for(int n, cudaStream_t st, CacheEntry* out) {
 
 }  // namespace
 
-// sums: [B][5] doubles, zeroed by the caller.  Returns the number of kernels launched, or -1.
-int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, double* sums, cudaStream_t st) {
+// blocks of the second product per frame = entries of `part` per frame
+int dct_energy_blocks(int H, int W) {
+    const int split_w = (W % 2 == 0 && W >= 4) ? 2 : 1;
+    return split_w * ((W / split_w + BN - 1) / BN) * ((H + BM - 1) / BM);
+}
+
+// sums: [B][5] doubles (overwritten); part: [B][dct_energy_blocks(H, W)][5] doubles of scratch.
+// Returns the number of kernels launched, or -1.
+int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, double* sums, double* part, cudaStream_t st) {
     CacheEntry ch, cw;
     if (matrices_for(H, st, &ch) || matrices_for(W, st, &cw)) return -1;
     DctArgs a;
-    a.G = grayf; a.T = tmp; a.Ah = ch.A; a.Btw = cw.Bt; a.sums = sums;
+    a.G = grayf; a.T = tmp; a.Ah = ch.A; a.Btw = cw.Bt; a.sums = sums; a.part = part;
     a.H = H; a.W = W; a.split_h = ch.split; a.split_w = cw.split;
     const int half_h = H / ch.split, half_w = W / cw.split;
     dct_rows_kernel<<<dim3((W + BN - 1) / BN, ch.split * ((half_h + BM - 1) / BM), B), GNT, 0, st>>>(a);
-    dct_cols_kernel<<<dim3(cw.split * ((half_w + BN - 1) / BN), (H + BM - 1) / BM, B), GNT, 0, st>>>(a);
-    return 2;
+    const dim3 g2(cw.split * ((half_w + BN - 1) / BN), (H + BM - 1) / BM, B);
+    dct_cols_kernel<<<g2, GNT, 0, st>>>(a);
+    dct_reduce_kernel<<<B, 32, 0, st>>>(part, (int)(g2.x * g2.y), sums);
+    return 3;
 }
 
 }  // namespace uwie

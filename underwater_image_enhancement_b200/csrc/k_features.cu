@@ -25,7 +25,8 @@
 #include "uwie_tables.h"
 
 namespace uwie {
-int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, double* sums, cudaStream_t st);
+int dct_energy_blocks(int H, int W);
+int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, double* sums, double* part, cudaStream_t st);
 int uwie_fail(int code, const std::string& msg);   // uwie_engine.cu
 }
 using namespace uwie;
@@ -42,7 +43,10 @@ struct FeAccum {                         // per frame, zeroed at the start of ev
     unsigned lbp[10];
     unsigned canny;
     unsigned sob_max_bits;               // float32 bit pattern of the largest Sobel magnitude (>= 0: integer order)
-    double sob_sum, sob_sq;
+    // Sobel magnitude sums as exact integers, so that the result does not depend on the order in which the blocks arrive:
+    // m (float32, 0 or in [2^-8, 2^3)) is a multiple of 2^-31; m * m (exact in float64) is a multiple of 2^-62 below 2^6,
+    // kept as floor(m * m * 2^30) and the 32 bits under it
+    unsigned long long sob_q, sob_sq_hi, sob_sq_lo;
     long long lap_abs, lap_sum, lap_sq;  // exact integer Laplacian sums
     double dct_total, dct_low, dct_mid, dct_high, dct_abs;
     double glcm[4][6];                   // per angle: contrast, dissimilarity, homogeneity, energy, correlation, ASM
@@ -105,7 +109,7 @@ __global__ void __launch_bounds__(NT) fe_stencil_kernel(const uint8_t* __restric
                                                         FeAccum* __restrict__ acc) {
     __shared__ int sg[ST + 2][ST + 2];
     __shared__ unsigned s_lbp[10];
-    __shared__ double s_red[NT / 32][2];
+    __shared__ unsigned long long s_red[NT / 32][3];
     __shared__ long long s_lred[NT / 32][3];
     __shared__ float s_max[NT / 32];
     const int b = blockIdx.z;
@@ -118,7 +122,7 @@ __global__ void __launch_bounds__(NT) fe_stencil_kernel(const uint8_t* __restric
         sg[ly][lx] = g[(size_t)y * W + x];
     }
     __syncthreads();
-    double sob = 0, sob2 = 0;
+    unsigned long long sob = 0, sob2_hi = 0, sob2_lo = 0;
     float smax = 0.f;
     long long la = 0, ls = 0, lq = 0;
     for (int i = threadIdx.x; i < ST * ST; i += NT) {
@@ -133,7 +137,14 @@ __global__ void __launch_bounds__(NT) fe_stencil_kernel(const uint8_t* __restric
         const float dx = __fdiv_rn((float)((a02 + 2 * a12 + a22) - (a00 + 2 * a10 + a20)), 255.0f);
         const float dy = __fdiv_rn((float)((a20 + 2 * a21 + a22) - (a00 + 2 * a01 + a02)), 255.0f);
         const float m = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
-        sob += (double)m; sob2 += (double)m * (double)m; smax = fmaxf(smax, m);
+        {
+            const double md = (double)m, sq = md * md * 1073741824.0;            // m * m * 2^30, exact
+            const double hi = floor(sq);
+            sob += (unsigned long long)(md * 2147483648.0);                       // m * 2^31, an integer
+            sob2_hi += (unsigned long long)hi;
+            sob2_lo += (unsigned long long)((sq - hi) * 4294967296.0);
+        }
+        smax = fmaxf(smax, m);
         // Laplacian ksize=3: [2 0 2; 0 -8 0; 2 0 2], exact integers
         const int lap = 2 * (a00 + a02 + a20 + a22) - 8 * a11;
         la += abs(lap); ls += lap; lq += (long long)lap * lap;
@@ -168,26 +179,27 @@ __global__ void __launch_bounds__(NT) fe_stencil_kernel(const uint8_t* __restric
         atomicAdd(&s_lbp[changes <= 2 ? __popc(bits) : 9], 1u);
     }
     // block reduction
-    sob = warp_sum_f64(sob); sob2 = warp_sum_f64(sob2);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
+        sob += __shfl_xor_sync(0xffffffffu, sob, o); sob2_hi += __shfl_xor_sync(0xffffffffu, sob2_hi, o);
+        sob2_lo += __shfl_xor_sync(0xffffffffu, sob2_lo, o);
         smax = fmaxf(smax, __shfl_xor_sync(0xffffffffu, smax, o));
         la += __shfl_xor_sync(0xffffffffu, la, o); ls += __shfl_xor_sync(0xffffffffu, ls, o); lq += __shfl_xor_sync(0xffffffffu, lq, o);
     }
     const int w = threadIdx.x >> 5;
     if ((threadIdx.x & 31) == 0) {
-        s_red[w][0] = sob; s_red[w][1] = sob2; s_max[w] = smax;
+        s_red[w][0] = sob; s_red[w][1] = sob2_hi; s_red[w][2] = sob2_lo; s_max[w] = smax;
         s_lred[w][0] = la; s_lred[w][1] = ls; s_lred[w][2] = lq;
     }
     __syncthreads();
     FeAccum& A = acc[b];
     if (threadIdx.x == 0) {
-        double t0 = 0, t1 = 0; float mx = 0.f; long long l0 = 0, l1 = 0, l2 = 0;
+        unsigned long long t0 = 0, t1 = 0, t2 = 0; float mx = 0.f; long long l0 = 0, l1 = 0, l2 = 0;
         for (int k = 0; k < NT / 32; ++k) {
-            t0 += s_red[k][0]; t1 += s_red[k][1]; mx = fmaxf(mx, s_max[k]);
+            t0 += s_red[k][0]; t1 += s_red[k][1]; t2 += s_red[k][2]; mx = fmaxf(mx, s_max[k]);
             l0 += s_lred[k][0]; l1 += s_lred[k][1]; l2 += s_lred[k][2];
         }
-        atomicAdd(&A.sob_sum, t0); atomicAdd(&A.sob_sq, t1);
+        atomicAdd(&A.sob_q, t0); atomicAdd(&A.sob_sq_hi, t1); atomicAdd(&A.sob_sq_lo, t2);
         atomicMax(&A.sob_max_bits, __float_as_uint(mx));
         atomicAdd((unsigned long long*)&A.lap_abs, (unsigned long long)l0);
         atomicAdd((unsigned long long*)&A.lap_sum, (unsigned long long)l1);
@@ -383,8 +395,10 @@ __global__ void __launch_bounds__(32) fe_final_kernel(const FeAccum* __restrict_
     }
     // ---- edge (FE:161-200)
     {
-        const double sm = A.sob_sum / n;
-        f[k++] = sm; f[k++] = sqrt(fmax(A.sob_sq / n - sm * sm, 0.0)); f[k++] = (double)__uint_as_float(A.sob_max_bits);
+        const double sob_sum = (double)A.sob_q * (1.0 / 2147483648.0);
+        const double sob_sq = (double)A.sob_sq_hi * (1.0 / 1073741824.0) + (double)A.sob_sq_lo * (1.0 / 4611686018427387904.0);
+        const double sm = sob_sum / n;
+        f[k++] = sm; f[k++] = sqrt(fmax(sob_sq / n - sm * sm, 0.0)); f[k++] = (double)__uint_as_float(A.sob_max_bits);
         f[k++] = (double)A.canny / n;
         const double lm = (double)A.lap_sum / n, lv = (double)A.lap_sq / n - lm * lm;
         f[k++] = (double)A.lap_abs / n; f[k++] = sqrt(fmax(lv, 0.0)); f[k++] = lv;
@@ -412,7 +426,7 @@ __global__ void fe_copy_canny_kernel(const unsigned* __restrict__ counts, FeAccu
     if (b < B) acc[b].canny = counts[b];
 }
 
-struct FeLayout { size_t ctab, acc, canny_counts, dct_sums, gray, grayf, tmp, thumb, glcm, labels, tile_list, tile_n, total; };
+struct FeLayout { size_t ctab, acc, canny_counts, dct_sums, dct_part, gray, grayf, tmp, thumb, glcm, labels, tile_list, tile_n, total; };
 FeLayout fe_layout(int B, int H, int W) {
     FeLayout L;
     size_t off = 0;
@@ -422,6 +436,7 @@ FeLayout fe_layout(int B, int H, int W) {
     L.acc = take((size_t)B * sizeof(FeAccum));
     L.canny_counts = take((size_t)B * 4);
     L.dct_sums = take((size_t)B * 5 * 8);
+    L.dct_part = take((size_t)B * dct_energy_blocks(H, W) * 5 * 8);
     L.gray = take(B * N);
     L.grayf = take(B * N * 4);
     L.tmp = take(B * N * 4);
@@ -510,7 +525,7 @@ int uwie_features79(const uint8_t* frames_dev, int batch, int height, int width,
 
     // DCT (k_dct.cu): D_H * G * D_W^T as hand-written float32 GEMMs with the even / odd butterfly; the coefficient plane is
     // never stored, its five sums land in dct_sums
-    if (launch_dct_energy(grayf, tmp, B, H, W, dct_sums, st) < 0)
+    if (launch_dct_energy(grayf, tmp, B, H, W, dct_sums, (double*)(ws + L.dct_part), st) < 0)
         return uwie_fail(UWIE_ERR_NOMEM, "uwie_features79: the cached DCT matrices could not be allocated");
     fe_copy_dct_kernel<<<(B + 127) / 128, 128, 0, st>>>(dct_sums, acc, B);
 

@@ -144,6 +144,9 @@ struct ApplyArgs {
     int var_n[4];                      // strategies per kernel variant (clahe * 2 + dehaze) and their indices:
     int var_s[4][kStrategiesMax];      // every variant is its own instantiation of apply_kernel
     int var_hist[4];                   // strategies of the variant that need the histogram pass (CLAHE + post-stretches)
+    int fin_n[4];                      // the same lists for the FINAL pass: a CLAHE strategy with post-stretches left its CLAHE
+    int fin_s[4][kStrategiesMax];      // output bytes in `out` during the histogram pass and finishes as variant 0 (tables only)
+    int from_out[kStrategiesMax];      // 1: the final pass reads `out` (in place) instead of the frame
     const uint8_t* frames;
     const StratTables* tables;
     const void* recovered;

@@ -515,7 +515,11 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     for (int i = 0; i < S; ++i) {
         const int v = (e->recipes[i].clahe ? 2 : 0) + (e->recipes[i].dehaze ? 1 : 0);
         aa.var_s[v][aa.var_n[v]++] = i;
-        if (e->recipes[i].clahe && e->recipes[i].n_post > 0) ++aa.var_hist[v];
+        const bool two_pass = e->recipes[i].clahe && e->recipes[i].n_post > 0;
+        if (two_pass) ++aa.var_hist[v];
+        const int fv = two_pass ? 0 : v;                   // the histogram pass leaves the CLAHE output in `out`
+        aa.fin_s[fv][aa.fin_n[fv]++] = i;
+        aa.from_out[i] = two_pass ? 1 : 0;
     }
     aa.frames = frames; aa.tables = sa.tables; aa.recovered = e->at<void>(L.recovered);
     aa.ctab = e->at<ColorTables>(L.ctab);
