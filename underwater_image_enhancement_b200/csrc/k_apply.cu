@@ -222,7 +222,7 @@ template <class T> struct Vec4 { T v[4][3]; };
 // CLAHE / DEHAZE: the strategy's path is fixed at compile time (one launch per variant present in the
 // library), so a pixel runs straight-line code and a kernel carries only its own path.
 template <class T, bool FINAL, bool CLAHE, bool DEHAZE>
-__global__ void __launch_bounds__(NT) apply_kernel(ApplyArgs a) {
+__global__ void __launch_bounds__(NT, (CLAHE && DEHAZE) ? 3 : 4) apply_kernel(ApplyArgs a) {
     constexpr int variant = (CLAHE ? 2 : 0) + (DEHAZE ? 1 : 0);
     const int s = FINAL ? a.fin_s[variant][blockIdx.y] : a.var_s[variant][blockIdx.y], b = blockIdx.z;
     const Recipe& rc = a.recipes[s];
