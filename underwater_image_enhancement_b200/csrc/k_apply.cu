@@ -47,6 +47,9 @@ __device__ __forceinline__ void stage_bytes(const ApplyArgs& a, const Recipe& rc
 // One block per (tile, strategy, frame).  Tables in shared memory, 4-pixel groups moved as words when the
 // tile lies inside the frame on 4-pixel boundaries (always at the BASELINE sizes); the clip / redistribute /
 // cumulative-sum tail runs on all 256 threads.
+// RGB -> Lab runs ONCE per pixel and strategy: this pass leaves the (L, a, b) bytes of every pixel in the strategy's
+// slot of `out`, and apply_kernel continues from them in place (no second conversion, and for the dehaze strategies
+// no second read of the float planes and no second pass through the pre-stretches).
 template <class T>
 __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
     const int s = blockIdx.y, b = blockIdx.z;
@@ -78,10 +81,15 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
     const size_t npix = (size_t)a.H * a.W;
     const uint8_t* frame = a.frames + (size_t)b * npix * 3;
     const T* rec = dehaze ? reinterpret_cast<const T*>(a.recovered) + (size_t)(b * a.n_dehaze + a.dehaze_slot[s]) * npix * 3 : nullptr;
-    auto count_bytes = [&](int r8, int g8, int b8) {
-        atomicAdd(&h[lab_L_only(s_gamma, s_cbrt, s_preq[0][r8], s_preq[1][g8], s_preq[2][b8])], 1u);
+    uint8_t* lab_out = a.out + ((size_t)b * a.S + s) * npix * 3;
+    // histogram entry + the pixel's Lab bytes packed as L | a << 8 | b << 16
+    auto count_bytes = [&](int r8, int g8, int b8) -> uint32_t {
+        int L, A, B;
+        rgb_to_lab(s_gamma, s_cbrt, s_preq[0][r8], s_preq[1][g8], s_preq[2][b8], L, A, B);
+        atomicAdd(&h[L], 1u);
+        return (uint32_t)L | ((uint32_t)A << 8) | ((uint32_t)B << 16);
     };
-    auto count_floats = [&](T v0, T v1, T v2) {
+    auto count_floats = [&](T v0, T v1, T v2) -> uint32_t {
         if (n_pre > 0) {
             v0 = stretch_apply_inv<T>(v0, lo[0][0], den[0][0], rden[0][0]); v1 = stretch_apply_inv<T>(v1, lo[0][1], den[0][1], rden[0][1]);
             v2 = stretch_apply_inv<T>(v2, lo[0][2], den[0][2], rden[0][2]);
@@ -90,12 +98,15 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
             v0 = stretch_apply_inv<T>(v0, lo[1][0], den[1][0], rden[1][0]); v1 = stretch_apply_inv<T>(v1, lo[1][1], den[1][1], rden[1][1]);
             v2 = stretch_apply_inv<T>(v2, lo[1][2], den[1][2], rden[1][2]);
         }
-        atomicAdd(&h[lab_L_only(s_gamma, s_cbrt, quantise<T>(v0), quantise<T>(v1), quantise<T>(v2))], 1u);
+        int L, A, B;
+        rgb_to_lab(s_gamma, s_cbrt, quantise<T>(v0), quantise<T>(v1), quantise<T>(v2), L, A, B);
+        atomicAdd(&h[L], 1u);
+        return (uint32_t)L | ((uint32_t)A << 8) | ((uint32_t)B << 16);
     };
     const int area = geo.tw * geo.th;
     const int y0 = tyi * geo.th, x0 = txi * geo.tw;
     const bool inside = y0 + geo.th <= a.H && x0 + geo.tw <= a.W && (geo.tw & 3) == 0 && (a.W & 3) == 0 &&
-                        (reinterpret_cast<uintptr_t>(frame) & 3) == 0 &&
+                        ((reinterpret_cast<uintptr_t>(frame) | reinterpret_cast<uintptr_t>(lab_out)) & 3) == 0 &&
                         (!dehaze || (sizeof(T) == 4 && (reinterpret_cast<uintptr_t>(rec) & 15) == 0 && (npix & 3) == 0));
     if (inside) {
         const int gpr = geo.tw >> 2;                       // 4-pixel groups per tile row
@@ -103,19 +114,22 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
         for (int i = threadIdx.x; i < groups; i += NT) {
             const int ly = i / gpr, gx = i - ly * gpr;
             const size_t p = (size_t)(y0 + ly) * a.W + x0 + 4 * gx;
+            uint32_t l0, l1, l2, l3;
             if (!dehaze) {
                 const uint32_t* w = reinterpret_cast<const uint32_t*>(frame + p * 3);
                 const uint32_t w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
-                count_bytes(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255);
-                count_bytes(w0 >> 24, w1 & 255, (w1 >> 8) & 255);
-                count_bytes((w1 >> 16) & 255, w1 >> 24, w2 & 255);
-                count_bytes((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24);
+                l0 = count_bytes(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255);
+                l1 = count_bytes(w0 >> 24, w1 & 255, (w1 >> 8) & 255);
+                l2 = count_bytes((w1 >> 16) & 255, w1 >> 24, w2 & 255);
+                l3 = count_bytes((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24);
             } else {
                 const float4* q = reinterpret_cast<const float4*>(rec + p * 3);
                 const float4 f0 = q[0], f1 = q[1], f2 = q[2];
-                count_floats((T)f0.x, (T)f0.y, (T)f0.z); count_floats((T)f0.w, (T)f1.x, (T)f1.y);
-                count_floats((T)f1.z, (T)f1.w, (T)f2.x); count_floats((T)f2.y, (T)f2.z, (T)f2.w);
+                l0 = count_floats((T)f0.x, (T)f0.y, (T)f0.z); l1 = count_floats((T)f0.w, (T)f1.x, (T)f1.y);
+                l2 = count_floats((T)f1.z, (T)f1.w, (T)f2.x); l3 = count_floats((T)f2.y, (T)f2.z, (T)f2.w);
             }
+            uint32_t* o = reinterpret_cast<uint32_t*>(lab_out + p * 3);
+            o[0] = l0 | (l1 << 24); o[1] = (l1 >> 8) | (l2 << 16); o[2] = (l2 >> 16) | (l3 << 8);
         }
     } else {
         for (int i = threadIdx.x; i < area; i += NT) {
@@ -123,9 +137,11 @@ __global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
             int y = y0 + ly, x = x0 + lx;
             if (y >= a.H) y = reflect101(y, a.H);          // cv2 pads the plane with REFLECT_101 up to a tile multiple
             if (x >= a.W) x = reflect101(x, a.W);
+            const bool own = y0 + ly < a.H && x0 + lx < a.W;      // a padded (reflected) position only counts
             const size_t p = (size_t)y * a.W + x;
-            if (!dehaze) count_bytes(frame[p * 3], frame[p * 3 + 1], frame[p * 3 + 2]);
-            else count_floats(rec[p * 3], rec[p * 3 + 1], rec[p * 3 + 2]);
+            const uint32_t l = !dehaze ? count_bytes(frame[p * 3], frame[p * 3 + 1], frame[p * 3 + 2])
+                                       : count_floats(rec[p * 3], rec[p * 3 + 1], rec[p * 3 + 2]);
+            if (own) { lab_out[p * 3] = (uint8_t)l; lab_out[p * 3 + 1] = (uint8_t)(l >> 8); lab_out[p * 3 + 2] = (uint8_t)(l >> 16); }
         }
     }
     __syncthreads();
@@ -220,9 +236,11 @@ struct ApplyShared {
 template <class T> struct Vec4 { T v[4][3]; };
 
 // CLAHE / DEHAZE: the strategy's path is fixed at compile time (one launch per variant present in the
-// library), so a pixel runs straight-line code and a kernel carries only its own path.
+// library), so a pixel runs straight-line code and a kernel carries only its own path.  A CLAHE strategy starts
+// from the Lab bytes clahe_lut_kernel left in its slot of `out` (whether or not a dehaze step came before: that
+// is all folded into those bytes), so CLAHE = true is only instantiated with DEHAZE = false.
 template <class T, bool FINAL, bool CLAHE, bool DEHAZE>
-__global__ void __launch_bounds__(NT, (CLAHE && DEHAZE) ? 3 : 4) apply_kernel(ApplyArgs a) {
+__global__ void __launch_bounds__(NT, 4) apply_kernel(ApplyArgs a) {
     constexpr int variant = (CLAHE ? 2 : 0) + (DEHAZE ? 1 : 0);
     const int s = FINAL ? a.fin_s[variant][blockIdx.y] : a.var_s[variant][blockIdx.y], b = blockIdx.z;
     const Recipe& rc = a.recipes[s];
@@ -267,7 +285,7 @@ __global__ void __launch_bounds__(NT, (CLAHE && DEHAZE) ? 3 : 4) apply_kernel(Ap
     }
     uint8_t* out = a.out + bs * (size_t)npix * 3;
     uint8_t* gray = FINAL ? a.gray + bs * (size_t)npix : nullptr;
-    const bool in_place = FINAL && !CLAHE && !DEHAZE && a.from_out[s] != 0;      // block-uniform
+    const bool in_place = CLAHE || (FINAL && !DEHAZE && a.from_out[s] != 0);     // block-uniform
     const uint8_t* frame = in_place ? out : a.frames + (size_t)b * npix * 3;
     const T* rec = dehaze ? reinterpret_cast<const T*>(a.recovered) + (size_t)(b * a.n_dehaze + a.dehaze_slot[s]) * npix * 3 : nullptr;
     const bool words_ok = ((reinterpret_cast<uintptr_t>(frame) | reinterpret_cast<uintptr_t>(out)) & 3) == 0 &&
@@ -290,15 +308,8 @@ __global__ void __launch_bounds__(NT, (CLAHE && DEHAZE) ? 3 : 4) apply_kernel(Ap
     // In the HIST pass q receives the CLAHE output bytes and f is not written.
     auto shade = [&](int r8, int g8, int b8, T fr, T fg, T fb, const ClaheRow& row, int x, T* f, int* q) -> bool {
         if (clahe) {
-            int r, g, bl, L, A, Bc;
-            if (!dehaze) { r = sm.preq[0][r8]; g = sm.preq[1][g8]; bl = sm.preq[2][b8]; }
-            else {
-                T v0 = fr, v1 = fg, v2 = fb;
-                pre_stretch(v0, v1, v2);
-                r = quantise<T>(v0); g = quantise<T>(v1); bl = quantise<T>(v2);
-            }
-            rgb_to_lab(sm.ct.gamma_in, sm.ct.cbrt_tab, r, g, bl, L, A, Bc);
-            L = clahe_interp(luts, tiles_x, inv_tw, row, x, L);
+            const int A = g8, Bc = b8;                   // the pixel's (L, a, b) bytes, see clahe_lut_kernel
+            const int L = clahe_interp(luts, tiles_x, inv_tw, row, x, r8);
             int k0, k1, k2;
             lab_to_rgb(sm.ct.lab_yf, sm.ct.gamma_out, L, A, Bc, k0, k1, k2);
             if (!FINAL) {
@@ -450,7 +461,7 @@ int launch_apply_t(const ApplyArgs& a, cudaStream_t st) {
             case 0: apply_kernel<T, FINAL, false, false><<<grid, NT, 0, st>>>(a); break;
             case 1: apply_kernel<T, FINAL, false, true><<<grid, NT, 0, st>>>(a); break;
             case 2: apply_kernel<T, FINAL, true, false><<<grid, NT, 0, st>>>(a); break;
-            default: apply_kernel<T, FINAL, true, true><<<grid, NT, 0, st>>>(a); break;
+            default: break;                                // variant 3 is never filled (see apply_kernel)
         }
         ++launches;
     }

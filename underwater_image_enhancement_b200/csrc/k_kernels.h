@@ -141,7 +141,7 @@ struct ApplyArgs {
     const Recipe* recipes;
     int n_dehaze;
     int dehaze_slot[kStrategiesMax];   // strategy -> slot in the recovered buffer, -1 if none
-    int var_n[4];                      // strategies per kernel variant (clahe * 2 + dehaze) and their indices:
+    int var_n[4];                      // strategies per kernel variant (0 tables only, 1 dehaze, 2 CLAHE) and their indices:
     int var_s[4][kStrategiesMax];      // every variant is its own instantiation of apply_kernel
     int var_hist[4];                   // strategies of the variant that need the histogram pass (CLAHE + post-stretches)
     int fin_n[4];                      // the same lists for the FINAL pass: a CLAHE strategy with post-stretches left its CLAHE

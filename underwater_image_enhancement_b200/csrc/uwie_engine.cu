@@ -513,7 +513,8 @@ int enqueue_batch(uwie_engine* e, const uint8_t* frames, int batch, uint8_t* out
     aa.n_dehaze = e->n_dehaze;
     for (int i = 0; i < kStrategiesMax; ++i) aa.dehaze_slot[i] = e->dehaze_slot[i];
     for (int i = 0; i < S; ++i) {
-        const int v = (e->recipes[i].clahe ? 2 : 0) + (e->recipes[i].dehaze ? 1 : 0);
+        // a CLAHE strategy continues from the Lab bytes of clahe_lut_kernel, with or without a dehaze step before: variant 2
+        const int v = e->recipes[i].clahe ? 2 : (e->recipes[i].dehaze ? 1 : 0);
         aa.var_s[v][aa.var_n[v]++] = i;
         const bool two_pass = e->recipes[i].clahe && e->recipes[i].n_post > 0;
         if (two_pass) ++aa.var_hist[v];
