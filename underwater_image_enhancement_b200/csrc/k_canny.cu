@@ -12,11 +12,11 @@
 //                          to one of its strong pixels (counted on the spot), P = other candidates that
 //                          reach a side shared with a neighbouring tile (pending).  Runs of P are linked by a
 //                          union-find in shared memory; each pending component goes to a short
-//                          per-tile list {root pixel, size}; the pixels on the tile's rim get a label
-//                          (edge / root pixel of a pending component / none) in the sparse label
-//                          plane — about 6 % of the plane is touched.
+//                          per-tile list (node k of the tile, its size); the 252 pixels on the tile's rim
+//                          get a label (edge / node of a pending component / none) in the tile's own
+//                          contiguous rim array - 1 KB per tile, no full-resolution label plane.
 //   2. canny_rim_kernel<false>  pending rim pixels link across tile borders (lock-free atomicMin
-//                          union-find on the root entries of the label plane).
+//                          union-find over the nodes, one entry per listed component).
 //   3. canny_rim_kernel<true>   a pending rim pixel next to a certain edge flags its global root.
 //   4. canny_list_kernel   listed components whose global root is flagged add their size.
 // A rectangle that fits one tile needs pass 1 only.
@@ -69,6 +69,9 @@ __device__ __forceinline__ Job make_job(const CannyArgs& a, int inst) {
 __device__ __forceinline__ int tile_slot() {
     return (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
 }
+// Scratch of one launch (CannyArgs::labels): rim labels [slots][RIM], then the union-find nodes [slots][kCannyListCap].
+// Node id = slot * kCannyListCap + k, k = position in the tile's list.
+__device__ __forceinline__ int total_slots() { return gridDim.x * gridDim.y * gridDim.z; }
 
 // ---- union-find on a label array (global or shared); label = smallest index of the component
 template <class P>
@@ -166,6 +169,13 @@ __device__ __forceinline__ void rim_pixel(int k, int& ly, int& lx) {
     else if (k < 2 * TW) { ly = TH - 1; lx = k - TW; }
     else if (k < 2 * TW + TH - 2) { ly = k - 2 * TW + 1; lx = 0; }
     else { ly = k - (2 * TW + TH - 2) + 1; lx = TW - 1; }
+}
+
+// inverse of rim_pixel for a pixel that lies on the rim
+__device__ __forceinline__ int rim_index(int ly, int lx) {
+    if (ly == 0) return lx;
+    if (ly == TH - 1) return TW + lx;
+    return lx == 0 ? 2 * TW + ly - 1 : 2 * TW + (TH - 2) + ly - 1;
 }
 
 // ---- pass 1
@@ -348,7 +358,8 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
 
     // ---- pending components: runs of P are the nodes of a union-find in shared memory (slab)
     const int slot = tile_slot();
-    int* lab = a.labels + (size_t)j.plane * npix;
+    int* rim = a.labels + (size_t)slot * RIM;
+    int* nodes = a.labels + (size_t)total_slots() * RIM;
     if (s_any) {                                                                // block-uniform
         // P is sparse: a thread owns the runs that START in one 16-column quarter of a tile row, so the
         // walks are short and all eight warps share them
@@ -379,32 +390,34 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
             atomicAdd(&slab[suf_find((volatile int*)slab, run_node(row, s0))], e0 - s0);
         }
         __syncthreads();
-        for (unsigned long long m = mystarts; m; m &= m - 1) {                  // roots -> list, nodes of the cross-tile union-find
+        for (unsigned long long m = mystarts; m; m &= m - 1) {                  // roots -> list = nodes of the cross-tile union-find
             const int s0 = __ffsll((long long)m) - 1;
             const int n = run_node(row, s0);
             const int w = slab[n];
             if ((w >> 16) != n) continue;
-            const int gp = (j.y0 + ty0 + row) * a.W + (j.x0 + tx0 + s0);
-            const int k = atomicAdd(&s_nlist, 1);
-            if (k < kCannyListCap) a.tile_list[(size_t)slot * kCannyListCap + k] = make_int2(gp, w & 0xffff);
-            lab[gp] = gp;
+            // every pending component holds a rim pixel and two of them are never adjacent on the ring: k < 126
+            const int k = min(atomicAdd(&s_nlist, 1), kCannyListCap - 1);       // (the bound above makes the clamp dead code)
+            const int id = slot * kCannyListCap + k;
+            a.tile_list[id] = make_int2(id, w & 0xffff);
+            nodes[id] = id;
+            slab[n] = (n << 16) | k;                                            // the size is stored: the low half now names the node
         }
+        __syncthreads();
     }
-    // ---- rim labels for the cross-tile passes: LAB_EDGE, root pixel of a pending component, or LAB_NONE
+    // ---- rim labels for the cross-tile passes: LAB_EDGE, node of a pending component, or LAB_NONE
     if (any_nb && tid < RIM) {
         int ly, lx;
         rim_pixel(tid, ly, lx);
-        const int ry = ty0 + ly, rx = tx0 + lx;
-        if (ry < rows && rx < cols) {
+        int v = LAB_NONE;
+        if (ty0 + ly < rows && tx0 + lx < cols) {
             const unsigned long long R = smp[ly];
-            int v = ((sme[ly] >> lx) & 1ull) ? LAB_EDGE : LAB_NONE;
-            if ((R >> lx) & 1ull) {
+            if ((sme[ly] >> lx) & 1ull) v = LAB_EDGE;
+            else if ((R >> lx) & 1ull) {
                 const int root = suf_find((volatile int*)slab, run_node(ly, run_start(R, lx)));
-                const int rrow = root >> 5;
-                v = (j.y0 + ty0 + rrow) * a.W + (j.x0 + tx0 + node_column(smp[rrow], root));
+                v = slot * kCannyListCap + (slab[root] & 0xffff);
             }
-            lab[(j.y0 + ry) * a.W + (j.x0 + rx)] = v;      // (a root on the rim gets its own index, as above)
         }
+        rim[tid] = v;
     }
     __syncthreads();
     if (tid == 0) a.tile_n[slot] = min(s_nlist, kCannyListCap);
@@ -417,17 +430,16 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
 //                 on the root entries of the label plane)
 //   FLAG = true : a pending pixel next to a certain edge -> its global root is flagged
 template <bool FLAG>
-__device__ __forceinline__ void rim_pair(int* lab, int p, int lp, int q) {
-    const int lq = lab[q];
+__device__ __forceinline__ void rim_pair(int* nodes, int lp, int lq) {
     if (!FLAG) {
-        if (lp >= 0 && lq >= 0) uf_union(lab, p, q);
+        if (lp >= 0 && lq >= 0) uf_union(nodes, lp, lq);
     } else {
         int t = -1;
-        if (lp >= 0 && lq == LAB_EDGE) t = p;
-        else if (lp == LAB_EDGE && lq >= 0) t = q;
+        if (lp >= 0 && lq == LAB_EDGE) t = lp;
+        else if (lp == LAB_EDGE && lq >= 0) t = lq;
         if (t >= 0) {
-            const int root = uf_find((volatile int*)lab, t);
-            if (!(lab[root] & LABEL_FLAG)) atomicOr(&lab[root], LABEL_FLAG);
+            const int root = uf_find((volatile int*)nodes, t);
+            if (!(nodes[root] & LABEL_FLAG)) atomicOr(&nodes[root], LABEL_FLAG);
         }
     }
 }
@@ -438,21 +450,27 @@ __global__ void __launch_bounds__(NT) canny_rim_kernel(CannyArgs a) {
     const int rows = j.y1 - j.y0, cols = j.x1 - j.x0;
     const int ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
     if (ty0 >= rows || tx0 >= cols || threadIdx.x >= RIM) return;
-    int* lab = a.labels + (size_t)j.plane * ((size_t)a.H * a.W);
     int ly, lx;
     rim_pixel(threadIdx.x, ly, lx);
     if (ly == TH - 1 && lx > 0 && lx < TW - 1) return;       // inner bottom row: all its earlier neighbours are in this tile
     const int ry = ty0 + ly, rx = tx0 + lx;
     if (ry >= rows || rx >= cols) return;
-    const int p = (j.y0 + ry) * a.W + (j.x0 + rx);
-    const int lp = lab[p];
+    const int slot = tile_slot();
+    const int lp = a.labels[(size_t)slot * RIM + threadIdx.x];
     if (lp == LAB_NONE) return;
-    if (lx == 0 && rx > 0) rim_pair<FLAG>(lab, p, lp, p - 1);
+    int* nodes = a.labels + (size_t)total_slots() * RIM;
+    // label of the pixel (ry + dy, rx + dx), which lies in another tile (and therefore on that tile's rim)
+    auto other = [&](int dy, int dx) -> int {
+        const int qy = ry + dy, qx = rx + dx;
+        const int by = qy / TH, bx = qx / TW;
+        const int qslot = (blockIdx.z * gridDim.y + by) * gridDim.x + bx;
+        return a.labels[(size_t)qslot * RIM + rim_index(qy - by * TH, qx - bx * TW)];
+    };
+    if (lx == 0 && rx > 0) rim_pair<FLAG>(nodes, lp, other(0, -1));
     if (ry > 0) {
-        const int up = p - a.W;
-        if ((lx == 0 || ly == 0) && rx > 0) rim_pair<FLAG>(lab, p, lp, up - 1);
-        if (ly == 0) rim_pair<FLAG>(lab, p, lp, up);
-        if ((ly == 0 || lx == TW - 1) && rx + 1 < cols) rim_pair<FLAG>(lab, p, lp, up + 1);
+        if ((lx == 0 || ly == 0) && rx > 0) rim_pair<FLAG>(nodes, lp, other(-1, -1));
+        if (ly == 0) rim_pair<FLAG>(nodes, lp, other(-1, 0));
+        if ((ly == 0 || lx == TW - 1) && rx + 1 < cols) rim_pair<FLAG>(nodes, lp, other(-1, 1));
     }
 }
 
@@ -465,12 +483,12 @@ __global__ void __launch_bounds__(kCannyListCap) canny_list_kernel(CannyArgs a) 
     const int slot = tile_slot();
     const int n = a.tile_n[slot];
     if (n == 0) return;                                       // block-uniform
-    int* lab = a.labels + (size_t)j.plane * ((size_t)a.H * a.W);
+    int* nodes = a.labels + (size_t)total_slots() * RIM;
     unsigned cnt = 0;
     if ((int)threadIdx.x < n) {
         const int2 e = a.tile_list[(size_t)slot * kCannyListCap + threadIdx.x];
-        const int root = uf_find((volatile int*)lab, e.x);
-        if (lab[root] & LABEL_FLAG) cnt = (unsigned)e.y;
+        const int root = uf_find((volatile int*)nodes, e.x);
+        if (nodes[root] & LABEL_FLAG) cnt = (unsigned)e.y;
     }
     cnt = warp_sum_u32(cnt);
     __shared__ unsigned sw[kCannyListCap / 32];
@@ -484,6 +502,8 @@ __global__ void __launch_bounds__(kCannyListCap) canny_list_kernel(CannyArgs a) 
 }
 
 }  // namespace
+
+size_t canny_label_bytes(size_t slots) { return slots * (size_t)(RIM + kCannyListCap) * sizeof(int); }
 
 size_t canny_tile_slots(int max_rows, int max_cols, int instances) {
     if (max_rows <= 0 || max_cols <= 0 || instances <= 0) return 0;

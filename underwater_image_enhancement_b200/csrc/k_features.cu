@@ -442,8 +442,8 @@ FeLayout fe_layout(int B, int H, int W) {
     L.tmp = take(B * N * 4);
     L.thumb = take((size_t)B * kThumb * kThumb);
     L.glcm = take((size_t)B * 4 * 65536 * 4);
-    L.labels = take(B * N * 4);
     const size_t slots = canny_tile_slots(H, W, B);
+    L.labels = take(canny_label_bytes(slots));
     L.tile_list = take(slots * kCannyListCap * sizeof(int2));
     L.tile_n = take(slots * 4);
     L.total = off;

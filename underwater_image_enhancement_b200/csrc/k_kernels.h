@@ -29,13 +29,14 @@ struct CannyArgs {
     const uint8_t* gray;        // [instances][H][W]
     int planes_per_img;
     // scratch + result
-    int* labels;                // [planes][H][W]   sparse: rim pixels of the tiles and roots of listed components
-    int2* tile_list;            // [tile slots][kCannyListCap]   {root pixel, size << 2 | strong | rim}
+    int* labels;                // canny_label_bytes(slots): rim labels [tile slots][252], then union-find nodes [tile slots][kCannyListCap]
+    int2* tile_list;            // [tile slots][kCannyListCap]   {node id, size}
     int* tile_n;                // [tile slots]
     unsigned* counts;           // QUADRANTS: [B][kQuadLevelsMax][4]; PLANES: [instances]
 };
 int launch_canny(const CannyArgs& a, int max_rows, int max_cols, int instances, cudaStream_t st);
 size_t canny_tile_slots(int max_rows, int max_cols, int instances);   // tile slots one launch uses
+size_t canny_label_bytes(size_t slots);                                 // bytes of CannyArgs::labels for that many slots
 
 // ------------------------------------------------------------------ k_stats.cu
 // per-channel 256-bin histograms of uint8 HWC frames: hist[B][3][256] (must be zeroed)

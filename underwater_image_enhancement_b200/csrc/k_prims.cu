@@ -836,8 +836,8 @@ LightLayout light_layout(int H, int W) {
     L.part = b.take((size_t)4 * kStatBlocks * 3 * 8);
     L.counts = b.take(kQuadLevelsMax * 4 * 4); L.quad_hist = b.take((size_t)kQuadLevelsMax * 4 * 768 * 4);
     L.trace = b.take(kQuadLevelsMax * 4 * 8);
-    L.labels = b.take(N * 4);
     const size_t slots = canny_tile_slots(H - H / 2, W - W / 2, 4);
+    L.labels = b.take(canny_label_bytes(slots));
     L.tile_list = b.take(slots * kCannyListCap * sizeof(int2)); L.tile_n = b.take(slots * 4);
     L.total = b.off;
     return L;
@@ -914,8 +914,8 @@ ScoreLayout score_layout(int H, int W) {
     L.q = b.take(N * 3); L.gray = b.take(N); L.rect = b.take(sizeof(QuadRect));
     L.sums = b.take(12 * 8); L.ssq = b.take(12 * 8); L.means = b.take(12 * 8);
     L.part = b.take((size_t)kStatBlocks * 3 * 8); L.count = b.take(256);
-    L.labels = b.take(N * 4);
     const size_t slots = canny_tile_slots(H, W, 1);
+    L.labels = b.take(canny_label_bytes(slots));
     L.tile_list = b.take(slots * kCannyListCap * sizeof(int2)); L.tile_n = b.take(slots * 4);
     L.total = b.off;
     return L;

@@ -92,8 +92,8 @@ QaLayout qa_layout(int B, int H, int W) {
     L.best = take((size_t)B * 4);
     L.cf_part = take((size_t)B * kQaBlocks * 4 * 8);
     L.gray = take(B * N);
-    L.labels = take(B * N * 4);
     const size_t slots = canny_tile_slots(H, W, B);
+    L.labels = take(canny_label_bytes(slots));
     L.tile_list = take(slots * kCannyListCap * sizeof(int2));
     L.tile_n = take(slots * 4);
     L.total = off;

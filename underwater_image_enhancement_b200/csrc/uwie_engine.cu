@@ -200,8 +200,8 @@ void plan_layout(uwie_engine* e) {
             slots = std::max(slots, canny_tile_slots(e->quad_dims[0].first, e->quad_dims[0].second, (int)(B * 4)));
         L.tile_list = b.take(slots * kCannyListCap * sizeof(int2));
         L.tile_n = b.take(slots * 4);
+        L.labels = b.take(canny_label_bytes(slots));
     }
-    L.labels = b.take(B * S * N * 4);
     L.ab = b.take(B * nd * 2 * N * 8);
     L.recovered = b.take(B * nd * N * 3 * tsz);
     L.targets = b.take(B * nd * kSelTargets * sizeof(SelTarget));
