@@ -255,6 +255,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         const int mx = tid % MW, chunk = tid / MW;
         if (chunk < 3) {
             const int my0 = chunk * CHUNK, my1 = min(my0 + CHUNK, MH);
+            const int sob_low = a.low;
             const int rx = tx0 + mx - 1;
             const bool col_in = rx >= 0 && rx < cols;
             // rows of this chunk that lie inside the rectangle: one unsigned compare per row
@@ -277,12 +278,15 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
                 const int ax = abs(dx), ay = abs(dy);
                 int v = 0;
                 if ((unsigned)(my - vlo) < vspan) {
-                    const int ys = ay << 15, tg22x = ax * 13573;
-                    int dir;
-                    if (ys < tg22x) dir = 0;
-                    else if (ys > tg22x + (ax << 16)) dir = 1;
-                    else dir = ((dx ^ dy) < 0) ? 2 : 3;
-                    v = (ax + ay) | (dir << 12);
+                    v = ax + ay;
+                    if (v > sob_low) {                   // the direction is only read for candidates (m > low): flat rows skip it
+                        const int ys = ay << 15, tg22x = ax * 13573;
+                        int dir;
+                        if (ys < tg22x) dir = 0;
+                        else if (ys > tg22x + (ax << 16)) dir = 1;
+                        else dir = ((dx ^ dy) < 0) ? 2 : 3;
+                        v |= dir << 12;
+                    }
                 }
                 sm[my][mx] = (uint16_t)v;
             }
