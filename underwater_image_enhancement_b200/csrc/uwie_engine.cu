@@ -81,18 +81,22 @@ struct uwie_engine {
     std::vector<cudaEvent_t> ev_pool;
     // two-slot pipeline of the host entry point
     struct HostPipe {
+        static constexpr int kLanes = 4;             // slots = lanes: chunk c uses slot c % slots and runs on lane c % lanes
         bool ready = false;
+        int slots = 0;                               // slots allocated so far (2 for a one-lane pipeline: double buffering)
         cudaStream_t s_in = nullptr, s_out = nullptr;
-        cudaEvent_t ev_in[2] = {}, ev_run[2] = {}, ev_out[2] = {}, ev_start = nullptr;
-        uint8_t* frames[2] = {}; uint8_t* best_img[2] = {}; uint8_t* out_all[2] = {}; char* small[2] = {};
+        cudaEvent_t ev_in[kLanes] = {}, ev_run[kLanes] = {}, ev_out[kLanes] = {}, ev_start = nullptr;
+        uint8_t* frames[kLanes] = {}; uint8_t* best_img[kLanes] = {}; uint8_t* out_all[kLanes] = {}; char* small[kLanes] = {};
         // pinned landing zone of the small results: a D2H copy into PAGEABLE memory blocks the host
         // until the stream gets there, which would serialise the whole pipeline
         char* h_small = nullptr; size_t h_small_frames = 0;
-        // second lane: odd chunks run on a twin engine (own workspace) and stream, so that the launch-
-        // and latency-bound stretches of one chunk (quadtree levels, table set-up, scoring) overlap the
-        // wide kernels of the other
-        uwie_engine* twin = nullptr; bool twin_failed = false;
-        cudaStream_t s_run2 = nullptr; cudaEvent_t ev_twin = nullptr;
+        // more lanes: chunk c runs on twin engine c % lanes (own workspace, own stream; lane 0 is this engine on the
+        // caller's stream), so that the launch- and latency-bound stretches of one chunk (quadtree levels, table
+        // set-up, the guided filter) overlap the wide kernels of the others - the same four lanes the device-resident
+        // bench runs
+        int lanes = 1;
+        uwie_engine* twin[kLanes] = {}; bool twin_failed = false;
+        cudaStream_t s_run[kLanes] = {}; cudaEvent_t ev_twin[kLanes] = {};
     } pipe;
     // CUDA graphs of the kernel sequence, one per (batch, pointer set): a step of the bench or of the host pipeline
     // presents the same few pointer sets again and again (chunk slices / the two slots), so the ~60 launches of a
@@ -358,7 +362,7 @@ void uwie_engine_destroy(uwie_engine* e) {
     if (e->owns_ws && e->ws) cudaFree(e->ws);
     {
         auto& hp = e->pipe;
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < uwie_engine::HostPipe::kLanes; ++k) {
             if (hp.frames[k]) cudaFree(hp.frames[k]);
             if (hp.best_img[k]) cudaFree(hp.best_img[k]);
             if (hp.out_all[k]) cudaFree(hp.out_all[k]);
@@ -366,14 +370,14 @@ void uwie_engine_destroy(uwie_engine* e) {
             if (hp.ev_in[k]) cudaEventDestroy(hp.ev_in[k]);
             if (hp.ev_run[k]) cudaEventDestroy(hp.ev_run[k]);
             if (hp.ev_out[k]) cudaEventDestroy(hp.ev_out[k]);
+            if (hp.twin[k]) uwie_engine_destroy(hp.twin[k]);
+            if (hp.s_run[k]) cudaStreamDestroy(hp.s_run[k]);
+            if (hp.ev_twin[k]) cudaEventDestroy(hp.ev_twin[k]);
         }
         if (hp.ev_start) cudaEventDestroy(hp.ev_start);
         if (hp.h_small) cudaFreeHost(hp.h_small);
         if (hp.s_in) cudaStreamDestroy(hp.s_in);
         if (hp.s_out) cudaStreamDestroy(hp.s_out);
-        if (hp.twin) uwie_engine_destroy(hp.twin);
-        if (hp.s_run2) cudaStreamDestroy(hp.s_run2);
-        if (hp.ev_twin) cudaEventDestroy(hp.ev_twin);
     }
     for (auto& m : e->marks) cudaEventDestroy(m.ev);
     for (auto& ev : e->ev_pool) cudaEventDestroy(ev);
@@ -382,7 +386,12 @@ void uwie_engine_destroy(uwie_engine* e) {
 }
 
 int uwie_engine_last_launches(const uwie_engine* e) { return e ? e->last_launches : 0; }
-long long uwie_engine_graph_replays(const uwie_engine* e) { return e ? e->graph_replays + (e->pipe.twin ? e->pipe.twin->graph_replays : 0) : 0; }
+long long uwie_engine_graph_replays(const uwie_engine* e) {
+    if (!e) return 0;
+    long long n = e->graph_replays;
+    for (int k = 1; k < uwie_engine::HostPipe::kLanes; ++k) if (e->pipe.twin[k]) n += e->pipe.twin[k]->graph_replays;
+    return n;
+}
 
 }  // extern "C"
 
@@ -679,23 +688,33 @@ int uwie_engine_host_prepare(uwie_engine* e, int max_count, int want_all, int wa
     if (max_count < 1) return fail(UWIE_ERR_ARG, "max_count must be positive");
     const size_t N = (size_t)e->H * e->W, S = e->S, B = e->B;
     uwie_engine::HostPipe& hp = e->pipe;
+    // lanes: one per chunk of the largest call, at most four (UWIE_HOST_LANES=n overrides, UWIE_HOST_ONE_LANE=1 forces one)
+    int want_lanes = (max_count + (int)B - 1) / (int)B;
+    if (want_lanes > uwie_engine::HostPipe::kLanes) want_lanes = uwie_engine::HostPipe::kLanes;
+    if (const char* v = std::getenv("UWIE_HOST_LANES")) {
+        const int n = std::atoi(v);
+        if (n >= 1 && n < want_lanes) want_lanes = n;
+    }
+    if (std::getenv("UWIE_HOST_ONE_LANE")) want_lanes = 1;
+    const int want_slots = want_lanes > 2 ? want_lanes : 2;
     if (!hp.ready) {
         CU(cudaStreamCreateWithFlags(&hp.s_in, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&hp.s_out, cudaStreamNonBlocking));
-        for (int k = 0; k < 2; ++k) {
-            CU(cudaEventCreateWithFlags(&hp.ev_in[k], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&hp.ev_run[k], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&hp.ev_out[k], cudaEventDisableTiming));
-            CU(cudaMalloc(&hp.frames[k], B * N * 3));
-            CU(cudaMalloc(&hp.small[k], B * (S * kScoreCols * 8 + 4 + 4 + 12) + 256));
-        }
         CU(cudaEventCreateWithFlags(&hp.ev_start, cudaEventDisableTiming));
         hp.ready = true;
     }
-    if (want_best && !hp.best_img[0])
-        for (int k = 0; k < 2; ++k) CU(cudaMalloc(&hp.best_img[k], B * N * 3));
-    if (want_all && !hp.out_all[0])                        // S times a chunk: only if somebody asks for it
-        for (int k = 0; k < 2; ++k) CU(cudaMalloc(&hp.out_all[k], B * S * N * 3));
+    for (int k = hp.slots; k < want_slots; ++k) {
+        CU(cudaEventCreateWithFlags(&hp.ev_in[k], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&hp.ev_run[k], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&hp.ev_out[k], cudaEventDisableTiming));
+        CU(cudaMalloc(&hp.frames[k], B * N * 3));
+        CU(cudaMalloc(&hp.small[k], B * (S * kScoreCols * 8 + 4 + 4 + 12) + 256));
+        hp.slots = k + 1;
+    }
+    for (int k = 0; k < hp.slots; ++k) {
+        if (want_best && !hp.best_img[k]) CU(cudaMalloc(&hp.best_img[k], B * N * 3));
+        if (want_all && !hp.out_all[k]) CU(cudaMalloc(&hp.out_all[k], B * S * N * 3));   // S times a chunk: only if somebody asks for it
+    }
     const size_t rec_bytes = S * kScoreCols * 8 + 4 + 4 + 12;
     if (hp.h_small_frames < (size_t)max_count) {
         if (hp.h_small) cudaFreeHost(hp.h_small);
@@ -703,14 +722,16 @@ int uwie_engine_host_prepare(uwie_engine* e, int max_count, int want_all, int wa
         CU(cudaMallocHost(&hp.h_small, (size_t)max_count * rec_bytes + 64));
         hp.h_small_frames = max_count;
     }
-    // second lane (see HostPipe): only worth its workspace when there is more than one chunk
-    if (max_count > (int)B && !hp.twin && !hp.twin_failed && !std::getenv("UWIE_HOST_ONE_LANE")) {
-        if (uwie_engine_create(&hp.twin, &e->pub_lib, e->pub_strategies.data(), (int)S, (int)B, e->H, e->W, nullptr, 0) != UWIE_OK ||
-            cudaStreamCreateWithFlags(&hp.s_run2, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreateWithFlags(&hp.ev_twin, cudaEventDisableTiming) != cudaSuccess) {
+    // twin engines (see HostPipe): only worth their workspaces when there is more than one chunk
+    for (int k = hp.lanes; k < want_lanes && !hp.twin_failed; ++k) {
+        if (uwie_engine_create(&hp.twin[k], &e->pub_lib, e->pub_strategies.data(), (int)S, (int)B, e->H, e->W, nullptr, 0) != UWIE_OK ||
+            cudaStreamCreateWithFlags(&hp.s_run[k], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&hp.ev_twin[k], cudaEventDisableTiming) != cudaSuccess) {
             cudaGetLastError();
-            if (hp.twin) { uwie_engine_destroy(hp.twin); hp.twin = nullptr; }
-            hp.twin_failed = true;                   // e.g. no memory for a second workspace: one lane it is
+            if (hp.twin[k]) { uwie_engine_destroy(hp.twin[k]); hp.twin[k] = nullptr; }
+            hp.twin_failed = true;                   // e.g. no memory for another workspace: the lanes so far it is
+        } else {
+            hp.lanes = k + 1;
         }
     }
     return UWIE_OK;
@@ -724,39 +745,40 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const size_t N = (size_t)e->H * e->W, S = e->S, B = e->B;
     uwie_engine::HostPipe& hp = e->pipe;
-    if (!hp.ready || hp.h_small_frames < (size_t)count || (out_all_host && !hp.out_all[0]) ||
-        (out_best_host && !hp.best_img[0]))
+    if (!hp.ready || hp.slots < 2 || hp.h_small_frames < (size_t)count || (out_all_host && !hp.out_all[hp.slots - 1]) ||
+        (out_best_host && !hp.best_img[hp.slots - 1]))
         return fail(UWIE_ERR_ARG, "uwie_enhance_score_host: call uwie_engine_host_prepare(engine, max_count, want_all, "
                                   "want_best) first (the call itself allocates nothing)");
     double* p_scores = reinterpret_cast<double*>(hp.h_small);
     int32_t* p_best = reinterpret_cast<int32_t*>(p_scores + (size_t)count * S * kScoreCols);
     int32_t* p_types = p_best + count;
     float* p_light = reinterpret_cast<float*>(p_types + count);
-    const bool two_lanes = hp.twin && !e->prof_on && count > (int)B;
+    const int lanes = (!e->prof_on && count > (int)B) ? hp.lanes : 1;
+    const int slots = lanes > 2 ? lanes : 2;
     // the copy streams must not start before work already queued on the caller's stream
     CU(cudaEventRecord(hp.ev_start, st));
     CU(cudaStreamWaitEvent(hp.s_in, hp.ev_start, 0));
     CU(cudaStreamWaitEvent(hp.s_out, hp.ev_start, 0));
-    if (two_lanes) CU(cudaStreamWaitEvent(hp.s_run2, hp.ev_start, 0));
+    for (int l = 1; l < lanes; ++l) CU(cudaStreamWaitEvent(hp.s_run[l], hp.ev_start, 0));
     int launches_total = 0;
     int chunk = 0;
     for (int done = 0; done < count; done += (int)B, ++chunk) {
-        const int k = chunk & 1;
+        const int k = chunk % slots, ln = chunk % lanes;
         const int nb = count - done < (int)B ? count - done : (int)B;
         double* d_scores = reinterpret_cast<double*>(hp.small[k]);
         int32_t* d_best = reinterpret_cast<int32_t*>(d_scores + B * S * kScoreCols);
         int32_t* d_types = d_best + B;
         float* d_light = reinterpret_cast<float*>(d_types + B);
-        // H2D: the slot's frames are free once the kernels of chunk - 2 are done
-        if (chunk >= 2) CU(cudaStreamWaitEvent(hp.s_in, hp.ev_run[k], 0));
+        // H2D: the slot's frames are free once the kernels of chunk - slots are done
+        if (chunk >= slots) CU(cudaStreamWaitEvent(hp.s_in, hp.ev_run[k], 0));
         CU(cudaMemcpyAsync(hp.frames[k], frames_host + (size_t)done * N * 3, (size_t)nb * N * 3,
                            cudaMemcpyHostToDevice, hp.s_in));
         CU(cudaEventRecord(hp.ev_in[k], hp.s_in));
-        // kernels: need the frames, and the slot's result buffers drained (D2H of chunk - 2)
-        uwie_engine* lane = (two_lanes && k) ? hp.twin : e;
-        cudaStream_t ls = (two_lanes && k) ? hp.s_run2 : st;
+        // kernels: need the frames, and the slot's result buffers drained (D2H of chunk - slots)
+        uwie_engine* lane = ln ? hp.twin[ln] : e;
+        cudaStream_t ls = ln ? hp.s_run[ln] : st;
         CU(cudaStreamWaitEvent(ls, hp.ev_in[k], 0));
-        if (chunk >= 2) CU(cudaStreamWaitEvent(ls, hp.ev_out[k], 0));
+        if (chunk >= slots) CU(cudaStreamWaitEvent(ls, hp.ev_out[k], 0));
         int rc = run_batch(lane, hp.frames[k], nb, out_all_host ? hp.out_all[k] : nullptr,
                            out_best_host ? hp.best_img[k] : nullptr, d_scores, d_best, d_types, d_light, ls);
         if (rc) return rc;
@@ -775,14 +797,14 @@ int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int coun
         if (light_host) CU(cudaMemcpyAsync(p_light + (size_t)done * 3, d_light, sizeof(float) * nb * 3, cudaMemcpyDeviceToHost, hp.s_out));
         CU(cudaEventRecord(hp.ev_out[k], hp.s_out));
     }
-    if (two_lanes) {                                  // the caller's stream is done when both lanes are
-        CU(cudaEventRecord(hp.ev_twin, hp.s_run2));
-        CU(cudaStreamWaitEvent(st, hp.ev_twin, 0));
+    for (int l = 1; l < lanes; ++l) {                 // the caller's stream is done when all lanes are
+        CU(cudaEventRecord(hp.ev_twin[l], hp.s_run[l]));
+        CU(cudaStreamWaitEvent(st, hp.ev_twin[l], 0));
     }
     CU(cudaStreamSynchronize(hp.s_out));
     e->last_launches = launches_total;
-    if (two_lanes) {
-        const int rc2 = uwie_engine_check(hp.twin, hp.s_run2);
+    for (int l = 1; l < lanes; ++l) {
+        const int rc2 = uwie_engine_check(hp.twin[l], hp.s_run[l]);
         if (rc2) return rc2;
     }
     if (scores_host) std::memcpy(scores_host, p_scores, sizeof(double) * (size_t)count * S * kScoreCols);
