@@ -109,8 +109,10 @@ int uwie_enhance_score(uwie_engine* e, const uint8_t* frames_dev, int batch,
  * memory makes the copies asynchronous with respect to the kernels of the neighbouring chunk.
  * The call allocates nothing: uwie_engine_host_prepare must have been called once with
  * max_count >= count and the want_* flags of the outputs that will be asked for (it owns the
- * double-buffered device slots, the pinned landing zone of the small results, the copy streams
- * and, when max_count > max_batch, the second lane's engine); otherwise UWIE_ERR_ARG.
+ * device slots, the pinned landing zone of the small results, the copy streams and, when max_count >
+ * max_batch, one further engine + stream per chunk of the largest call, up to four lanes in all: chunk c
+ * runs on lane c % lanes, so the latency-bound stretches of one chunk overlap the wide kernels of the
+ * others; UWIE_HOST_LANES=n caps the lanes); otherwise UWIE_ERR_ARG.
  * This is the loop body of main.py:88-155 / six_stadigy.py:392-447 without the file I/O. */
 int uwie_engine_host_prepare(uwie_engine* e, int max_count, int want_all, int want_best);
 int uwie_enhance_score_host(uwie_engine* e, const uint8_t* frames_host, int count,
