@@ -40,7 +40,9 @@ def test_features_match_reference_fixture():
         _check(got, want, (int(seed), int(h), int(w)))
 
 
-@pytest.mark.parametrize("shape", [(33, 250), (97, 131), (2, 2), (1080, 1920)])
+# (33, 250), (97, 131), (2, 2): a dimension with another prime factor (or too short) -> the DCT as matrix products;
+# the others factor into 2, 3 and 5 -> the DCT through shared-memory FFTs (k_dct_fft.cu), odd lengths included
+@pytest.mark.parametrize("shape", [(33, 250), (97, 131), (2, 2), (1080, 1920), (90, 150), (45, 125), (720, 1280), (8, 4096)])
 def test_features_batch_matches_oracle(shape):
     h, w = shape
     frames = np.stack([synth_image(s, h, w) for s in (21, 22, 23)])
@@ -53,8 +55,8 @@ def test_float_input_and_groups():
     frame = synth_image(4, 96, 128)
     img = frame.astype(np.float32) / 255.0                       # main.py:108
     full = F.FeatureExtractor.extract_all_features(img)
-    # double atomics make the last bits of the float sums run-dependent
-    assert np.allclose(full, F.FeatureExtractor.extract_all_features(frame), rtol=1e-12, atol=1e-12)
+    # every sum is formed in a fixed order: the same bits run after run, from bytes or from the float image
+    assert np.array_equal(full, F.FeatureExtractor.extract_all_features(frame))
     parts = [F.FeatureExtractor.extract_color_features(img), F.FeatureExtractor.extract_texture_features(img),
              F.FeatureExtractor.extract_frequency_features(img), F.FeatureExtractor.extract_edge_features(img),
              F.FeatureExtractor.extract_quality_features(img)]

@@ -21,7 +21,7 @@ LIB = os.path.join(PKG, "libuwie_b200.so")
 HOSTCHECK = os.path.join(ROOT, "tests", "_hostcheck.so")
 
 CU_SOURCES = ("k_stats.cu", "k_setup.cu", "k_canny.cu", "k_quadtree.cu", "k_guided.cu", "k_select.cu",
-              "k_apply.cu", "k_score.cu", "k_vgg.cu", "k_features.cu", "k_qa.cu", "k_prims.cu", "k_dct.cu", "uwie_engine.cu")
+              "k_apply.cu", "k_score.cu", "k_vgg.cu", "k_features.cu", "k_qa.cu", "k_prims.cu", "k_dct.cu", "k_dct_fft.cu", "uwie_engine.cu")
 CPP_SOURCES = ("uwie_tables.cpp",)
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

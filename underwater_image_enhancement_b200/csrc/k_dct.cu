@@ -12,6 +12,7 @@
 // The half matrices are built once per (device, n) and cached.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <utility>
@@ -250,15 +251,37 @@ int matrices_for(int n, cudaStream_t st, CacheEntry* out) {
 
 }  // namespace
 
-// blocks of the second product per frame = entries of `part` per frame
+// k_dct_fft.cu: the same five sums through shared-memory FFTs, for sizes that factor into 2, 3 and 5
+bool dct_fft_usable(int H, int W);
+int dct_fft_blocks(int W);
+int launch_dct_fft(const float* grayf, float* tmp, int B, int H, int W, double* part, cudaStream_t st);
+
+namespace {
+// UWIE_DCT_GEMM=1 keeps the matrix form for every size (comparison runs, tests)
+bool use_fft(int H, int W) {
+    static const bool forced_gemm = [] { const char* v = std::getenv("UWIE_DCT_GEMM"); return v && v[0] == '1'; }();
+    return !forced_gemm && dct_fft_usable(H, W);
+}
+}  // namespace
+
+// blocks of the reducing pass per frame = entries of `part` per frame (the larger of the two forms: the choice can be
+// overridden at run time)
 int dct_energy_blocks(int H, int W) {
     const int split_w = (W % 2 == 0 && W >= 4) ? 2 : 1;
-    return split_w * ((W / split_w + BN - 1) / BN) * ((H + BM - 1) / BM);
+    const int gemm = split_w * ((W / split_w + BN - 1) / BN) * ((H + BM - 1) / BM);
+    const int fft = dct_fft_usable(H, W) ? dct_fft_blocks(W) : 0;
+    return gemm > fft ? gemm : fft;
 }
 
 // sums: [B][5] doubles (overwritten); part: [B][dct_energy_blocks(H, W)][5] doubles of scratch.
 // Returns the number of kernels launched, or -1.
 int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, double* sums, double* part, cudaStream_t st) {
+    if (use_fft(H, W)) {
+        const int k = launch_dct_fft(grayf, tmp, B, H, W, part, st);
+        if (k < 0) return -1;
+        dct_reduce_kernel<<<B, 32, 0, st>>>(part, dct_fft_blocks(W), sums);
+        return k + 1;
+    }
     CacheEntry ch, cw;
     if (matrices_for(H, st, &ch) || matrices_for(W, st, &cw)) return -1;
     DctArgs a;
