@@ -214,13 +214,15 @@ __global__ void __launch_bounds__(GNT, 2) dct_cols_kernel(DctArgs a) {
     }
 }
 
-// the block sums of one frame in block order: the five results do not depend on how the blocks were scheduled
+// the block sums of one frame in a fixed order (lane l adds entries l, l + 32, ...; then a fixed shuffle tree): the five
+// results do not depend on how the blocks were scheduled.  One warp per (frame, sum).
 __global__ void dct_reduce_kernel(const double* __restrict__ part, int nblk, double* __restrict__ sums) {
-    const int b = blockIdx.x;
-    if (threadIdx.x >= 5) return;
+    const int b = blockIdx.x, k = threadIdx.y, lane = threadIdx.x;
     double s = 0;
-    for (int i = 0; i < nblk; ++i) s += part[((size_t)b * nblk + i) * 5 + threadIdx.x];
-    sums[(size_t)b * 5 + threadIdx.x] = s;
+    for (int i = lane; i < nblk; i += 32) s += part[((size_t)b * nblk + i) * 5 + k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if (lane == 0) sums[(size_t)b * 5 + k] = s;
 }
 
 struct CacheEntry { float* A; float* Bt; int split; };
@@ -279,7 +281,7 @@ int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, doubl
     if (use_fft(H, W)) {
         const int k = launch_dct_fft(grayf, tmp, B, H, W, part, st);
         if (k < 0) return -1;
-        dct_reduce_kernel<<<B, 32, 0, st>>>(part, dct_fft_blocks(W), sums);
+        dct_reduce_kernel<<<B, dim3(32, 5), 0, st>>>(part, dct_fft_blocks(W), sums);
         return k + 1;
     }
     CacheEntry ch, cw;
@@ -291,7 +293,7 @@ int launch_dct_energy(const float* grayf, float* tmp, int B, int H, int W, doubl
     dct_rows_kernel<<<dim3((W + BN - 1) / BN, ch.split * ((half_h + BM - 1) / BM), B), GNT, 0, st>>>(a);
     const dim3 g2(cw.split * ((half_w + BN - 1) / BN), (H + BM - 1) / BM, B);
     dct_cols_kernel<<<g2, GNT, 0, st>>>(a);
-    dct_reduce_kernel<<<B, 32, 0, st>>>(part, (int)(g2.x * g2.y), sums);
+    dct_reduce_kernel<<<B, dim3(32, 5), 0, st>>>(part, (int)(g2.x * g2.y), sums);
     return 3;
 }
 
