@@ -93,7 +93,7 @@ __device__ __forceinline__ Strip make_strip(const GuidedArgs& a, int r) {
 }
 
 // ------------------------------------------------------------------ a, b
-template <bool CLIP, bool FAST>
+template <bool CLIP, bool FAST, class AB>
 __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a) {
     __shared__ double sP[GWARPS][GSPAN];
     __shared__ double sGP[GWARPS][GSPAN];
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a
     const double eps = rc.eps;
     const unsigned npix = (unsigned)a.H * a.W;
     const uint2* gd = a.gd_plane + (size_t)b * npix;
-    double2* pab = a.ab + (size_t)inst * npix;
+    AB* pab = reinterpret_cast<AB*>(a.ab) + (size_t)inst * npix;
     const double rr = (double)s.r * (double)s.r;
     const double scale = 1.0 / rr;                       // cv2: sum * (1 / (kw * kh))
     const double scale_i = 1.0 / (255.0 * rr), scale_ii = 1.0 / (65025.0 * rr);
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a
             const int c = min(base + i, GSPAN - 1);
             hp += wP[c]; hgp += wGP[c]; hg += wG[c];
         }
-        double2* orow = pab + (unsigned)yo * (unsigned)a.W + (unsigned)(s.xs + base);
+        AB* orow = pab + (unsigned)yo * (unsigned)a.W + (unsigned)(s.xs + base);
 #pragma unroll
         for (int j = 0; j < GC; ++j) {
             if (j > 0) {
@@ -202,7 +202,10 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a
             // FAST: eps >= 1e-9, so den is normal and |a| < 1e10 (a is 0 or far above the subnormals)
             const double ra = FAST ? div_rn_normal(cov, den) : __ddiv_rn(cov, den);
             const double rb = __dsub_rn(mP, __dmul_rn(ra, mI));
-            if (base + j < s.outw && s.xs + base + j < a.W) orow[j] = make_double2(ra, rb);
+            if (base + j < s.outw && s.xs + base + j < a.W) {
+                if (sizeof(AB) == 16) *reinterpret_cast<double2*>(&orow[j]) = make_double2(ra, rb);
+                else *reinterpret_cast<float2*>(&orow[j]) = make_float2((float)ra, (float)rb);
+            }
         }
         __syncwarp();
         row_out(L);
@@ -220,7 +223,7 @@ struct RecoverShared {
     float sdiff[3][256];                // img - A, float32              SS:185, ES:247
     unsigned shist[3 * kSelBinsA];
 };
-template <class T>
+template <class T, class AB>
 __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_recover_kernel(GuidedArgs a) {
     // dynamic shared memory (57 KB, above the static limit), see RecoverShared
     extern __shared__ __align__(16) unsigned char gf_smem[];
@@ -246,7 +249,7 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_recover_kernel(GuidedA
     if (s.valid) {
         const unsigned npix = (unsigned)a.H * a.W;
         const uint2* gd = a.gd_plane + (size_t)b * npix;
-        const double2* pab = a.ab + (size_t)inst * npix;
+        const AB* pab = reinterpret_cast<const AB*>(a.ab) + (size_t)inst * npix;
         T* out = reinterpret_cast<T*>(a.recovered) + (size_t)inst * npix * 3;
         const double scale = 1.0 / ((double)s.r * (double)s.r);
         double* wA = sm.sA[s.warp]; double* wB = sm.sB[s.warp];
@@ -261,23 +264,23 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_recover_kernel(GuidedA
         for (int j = 0; j < GC; ++j) { va[j] = 0.0; vb[j] = 0.0; }
         // row loads: both are requested right before the long recovery step of a row, the entering
         // row for the NEXT step and the leaving row for this one (consumed after that step)
-        double2 E[GC], L[GC];
-        auto row_load = [&](int yy, double2 (&q)[GC]) {
-            const double2* rowp = pab + (unsigned)reflect101(yy, a.H) * (unsigned)a.W;   // warp-uniform
+        AB E[GC], L[GC];
+        auto row_load = [&](int yy, AB (&q)[GC]) {
+            const AB* rowp = pab + (unsigned)reflect101(yy, a.H) * (unsigned)a.W;   // warp-uniform
 #pragma unroll
             for (int j = 0; j < GC; ++j) q[j] = __ldg(rowp + cx[j]);
         };
         for (int yy = s.ys - s.lo; yy < s.ys + s.hi; ++yy) {
             row_load(yy, E);
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] += E[j].x; vb[j] += E[j].y; }
+            for (int j = 0; j < GC; ++j) { va[j] += (double)E[j].x; vb[j] += (double)E[j].y; }
         }
         const int base = s.lane * GC;
         const int nblocks = s.r / GC;
         row_load(s.ys + s.hi, E);
         for (int yo = s.ys; yo < s.ye; ++yo) {
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] += E[j].x; vb[j] += E[j].y; }
+            for (int j = 0; j < GC; ++j) { va[j] += (double)E[j].x; vb[j] += (double)E[j].y; }
             // this row's pixels (frame bytes + gray) for the recovery step below, requested early
             const unsigned ro = (unsigned)yo * (unsigned)a.W;
             unsigned pixw[GC];
@@ -361,7 +364,7 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_recover_kernel(GuidedA
             }
             __syncwarp();
 #pragma unroll
-            for (int j = 0; j < GC; ++j) { va[j] -= L[j].x; vb[j] -= L[j].y; }
+            for (int j = 0; j < GC; ++j) { va[j] -= (double)L[j].x; vb[j] -= (double)L[j].y; }
         }
     }
     __syncthreads();
@@ -458,25 +461,34 @@ int launch_guided(const GuidedArgs& a0, int max_radius, cudaStream_t st) {
     }
     const int chunks = (a.H + a.rows_per_block - 1) / a.rows_per_block;
     dim3 grid(bx, chunks, inst);
+    // UWIE_GF_AB32=1 (experiment): the {a, b} pairs cross HBM as float32 instead of float64
+    static const bool ab32 = [] { const char* v = std::getenv("UWIE_GF_AB32"); return v && v[0] == '1'; }();
     static const bool optin = [] {
         const int most = 128 * 1024, most_r = (int)sizeof(RecoverShared) + 120 * 1024;   // + static: below the 227 KB of an SM
-        return cudaFuncSetAttribute(gf_recover_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, most_r) == cudaSuccess &&
-               cudaFuncSetAttribute(gf_recover_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, most_r) == cudaSuccess &&
-               cudaFuncSetAttribute(gf_ab_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
-               cudaFuncSetAttribute(gf_ab_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
-               cudaFuncSetAttribute(gf_ab_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
-               cudaFuncSetAttribute(gf_ab_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess;
+        return cudaFuncSetAttribute(gf_recover_kernel<double, double2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most_r) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_recover_kernel<float, double2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most_r) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_recover_kernel<float, float2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most_r) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<true, true, double2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<true, true, float2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<true, false, double2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<false, true, double2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess &&
+               cudaFuncSetAttribute(gf_ab_kernel<false, false, double2>, cudaFuncAttributeMaxDynamicSharedMemorySize, most) == cudaSuccess;
     }();
     (void)optin;                                        // a failure shows up as a launch error below
-    if (a.lib.clip_t0) {
-        if (a.eps_safe) gf_ab_kernel<true, true><<<grid, nt, pad, st>>>(a);
-        else gf_ab_kernel<true, false><<<grid, nt, pad, st>>>(a);
-    } else {
-        if (a.eps_safe) gf_ab_kernel<false, true><<<grid, nt, pad, st>>>(a);
-        else gf_ab_kernel<false, false><<<grid, nt, pad, st>>>(a);
+    if (ab32 && a.lib.clip_t0 && a.eps_safe && !a.lib.f64) {
+        gf_ab_kernel<true, true, float2><<<grid, nt, pad, st>>>(a);
+        gf_recover_kernel<float, float2><<<grid, nt, sizeof(RecoverShared) + pad, st>>>(a);
+        return 3;
     }
-    if (a.lib.f64) gf_recover_kernel<double><<<grid, nt, sizeof(RecoverShared) + pad, st>>>(a);
-    else gf_recover_kernel<float><<<grid, nt, sizeof(RecoverShared) + pad, st>>>(a);
+    if (a.lib.clip_t0) {
+        if (a.eps_safe) gf_ab_kernel<true, true, double2><<<grid, nt, pad, st>>>(a);
+        else gf_ab_kernel<true, false, double2><<<grid, nt, pad, st>>>(a);
+    } else {
+        if (a.eps_safe) gf_ab_kernel<false, true, double2><<<grid, nt, pad, st>>>(a);
+        else gf_ab_kernel<false, false, double2><<<grid, nt, pad, st>>>(a);
+    }
+    if (a.lib.f64) gf_recover_kernel<double, double2><<<grid, nt, sizeof(RecoverShared) + pad, st>>>(a);
+    else gf_recover_kernel<float, double2><<<grid, nt, sizeof(RecoverShared) + pad, st>>>(a);
     return 3;
 }
 
