@@ -166,15 +166,26 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a
         double hp = 0.0, hgp = 0.0;
         unsigned long long hg = 0ull;
         {
-            double bp = 0.0, bgp = 0.0;
-            unsigned long long bg = 0ull;
-#pragma unroll
-            for (int j = 0; j < GC; ++j) { bp += wP[base + j]; bgp += wGP[base + j]; bg += wG[base + j]; }
+            // (these sums are exact, so their order is free: pairs first, and the neighbours' block sums are fetched
+            // before any of them is added - the dependency chain of a row is what bounds this kernel)
+            static_assert(GC == 5, "block sums are written out for five columns");
+            const double bp = ((wP[base] + wP[base + 1]) + (wP[base + 2] + wP[base + 3])) + wP[base + 4];
+            const double bgp = ((wGP[base] + wGP[base + 1]) + (wGP[base + 2] + wGP[base + 3])) + wGP[base + 4];
+            const unsigned long long bg = ((wG[base] + wG[base + 1]) + (wG[base + 2] + wG[base + 3])) + wG[base + 4];
             if (nblocks > 0) { hp = bp; hgp = bgp; hg = bg; }
-            for (int t = 1; t < nblocks; ++t) {                   // warp-uniform trip count
-                hp += __shfl_down_sync(0xffffffffu, bp, t);
-                hgp += __shfl_down_sync(0xffffffffu, bgp, t);
-                hg += __shfl_down_sync(0xffffffffu, bg, t);
+            if (nblocks >= 2 && nblocks <= 4) {                   // r = 10 .. 24: the radii of both libraries
+                const double p1 = __shfl_down_sync(0xffffffffu, bp, 1), p2 = __shfl_down_sync(0xffffffffu, bp, 2), p3 = __shfl_down_sync(0xffffffffu, bp, 3);
+                const double q1 = __shfl_down_sync(0xffffffffu, bgp, 1), q2 = __shfl_down_sync(0xffffffffu, bgp, 2), q3 = __shfl_down_sync(0xffffffffu, bgp, 3);
+                const unsigned long long g1 = __shfl_down_sync(0xffffffffu, bg, 1), g2 = __shfl_down_sync(0xffffffffu, bg, 2), g3 = __shfl_down_sync(0xffffffffu, bg, 3);
+                hp = bp + p1; hgp = bgp + q1; hg = bg + g1;
+                if (nblocks == 3) { hp += p2; hgp += q2; hg += g2; }
+                if (nblocks == 4) { hp += p2 + p3; hgp += q2 + q3; hg += g2 + g3; }
+            } else {
+                for (int t = 1; t < nblocks; ++t) {               // warp-uniform trip count
+                    hp += __shfl_down_sync(0xffffffffu, bp, t);
+                    hgp += __shfl_down_sync(0xffffffffu, bgp, t);
+                    hg += __shfl_down_sync(0xffffffffu, bg, t);
+                }
             }
         }
         // Every lane forms all 5 outputs in straight-line code (dead ones from clamped reads) so that the
@@ -184,14 +195,26 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a
             hp += wP[c]; hgp += wGP[c]; hg += wG[c];
         }
         AB* orow = pab + (unsigned)yo * (unsigned)a.W + (unsigned)(s.xs + base);
+        // windows of outputs 1 .. 4 = window 0 + what entered - what left; the differences do not depend on each other
+        double dP[GC], dGP[GC];
+        unsigned long long dG[GC];
+        dP[0] = 0.0; dGP[0] = 0.0; dG[0] = 0ull;
+#pragma unroll
+        for (int j = 1; j < GC; ++j) {
+            const int in = min(base + j + s.r - 1, GSPAN - 1);
+            dP[j] = wP[in] - wP[base + j - 1];
+            dGP[j] = wGP[in] - wGP[base + j - 1];
+            dG[j] = wG[in] - wG[base + j - 1];
+        }
+        dP[2] += dP[1]; dGP[2] += dGP[1]; dG[2] += dG[1];
+        dP[4] += dP[3]; dGP[4] += dGP[3]; dG[4] += dG[3];
+        dP[3] += dP[2]; dGP[3] += dGP[2]; dG[3] += dG[2];
+        dP[4] += dP[2]; dGP[4] += dGP[2]; dG[4] += dG[2];
+        const double hp0 = hp, hgp0 = hgp;
+        const unsigned long long hg0 = hg;
 #pragma unroll
         for (int j = 0; j < GC; ++j) {
-            if (j > 0) {
-                const int in = min(base + j + s.r - 1, GSPAN - 1);
-                hp += wP[in] - wP[base + j - 1];
-                hgp += wGP[in] - wGP[base + j - 1];
-                hg += wG[in] - wG[base + j - 1];
-            }
+            hp = hp0 + dP[j]; hgp = hgp0 + dGP[j]; hg = hg0 + dG[j];
             const double mI = (double)(unsigned)(hg >> 32) * scale_i;
             const double mII = (double)(unsigned)(hg & 0xffffffffull) * scale_ii;
             const double mP = hp * scale;
