@@ -3,7 +3,7 @@ pool and stays closed"; gpurun refuses it).  Two in-process substitutes, wired i
 Python faces (_lib.scratch):
 
   * initcheck's question — does any result depend on scratch memory that was never written?  Every workspace, the
-    engine's included (its Canny label plane is deliberately never cleared), is filled with 0x00, 0xFF and 0xA5 before
+    engine's included (its Canny rim-label / node arrays are deliberately never cleared), is filled with 0x00, 0xFF and 0xA5 before
     use; all results must be bit-identical across the three fills.
   * memcheck's question — does any kernel write outside the bytes `*_workspace_bytes` promised?  Every workspace sits
     between two 4 KiB canary bands that must come back untouched.
