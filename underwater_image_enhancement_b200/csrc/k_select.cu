@@ -205,27 +205,30 @@ __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
             const unsigned ka = key[j] >> 21;
             if (ka <= 1024u && ps.hot[j % 3][ka] != 0) hot |= 1u << j;
         }
-        if (__ballot_sync(0xffffffffu, hot != 0) == 0) continue;     // the common case
+        // A hot value is rare per LANE (the targets' level-A bins hold ~1 % of the data) but not per warp (384 values a
+        // round): the lanes that hold one take this branch alone and meet whoever else is there (__activemask), instead
+        // of all 32 lanes walking every value slot and every target behind warp-wide ballots.
+        if (hot != 0) {
 #pragma unroll
-        for (int j = 0; j < 3 * PER; ++j) {
-            const int c = j % 3;
-            const bool hc = (hot >> j) & 1u;
-            if (__ballot_sync(0xffffffffu, hc) == 0) continue;
-            const unsigned hi = key[j] >> SHIFT, sub = (key[j] >> SUBSHIFT) & SUBMASK;
-            const int nt = ps.cnt[c];                            // uniform
+            for (int j = 0; j < 3 * PER; ++j) {
+                if (!((hot >> j) & 1u)) continue;
+                const int c = j % 3;
+                const unsigned hi = key[j] >> SHIFT, sub = (key[j] >> SUBSHIFT) & SUBMASK;
+                const int nt = ps.cnt[c];
 #pragma unroll 1
-            for (int t = 0; t < nt; ++t) {
-                const int tg = ps.list[c][t];
-                const bool hit = hc && ps.pre[tg] == hi;
-                const unsigned hits = __ballot_sync(0xffffffffu, hit);
-                if (hit) {
-                    agg_add(gh + (size_t)tg * BINS, sub, hits);
+                for (int t = 0; t < nt; ++t) {
+                    const int tg = ps.list[c][t];
+                    if (ps.pre[tg] != hi) continue;
+                    const int lane = threadIdx.x & 31;
+                    const unsigned peers = __match_any_sync(__activemask(), (unsigned)tg);     // lanes here for the same target
+                    const unsigned same = __match_any_sync(peers, sub);                         // ... and the same bin: one atomic
+                    if ((int)(__ffs(same) - 1) == lane) atomicAdd(gh + (size_t)tg * BINS + sub, (unsigned)__popc(same));
                     if (LEVEL == 1) {
-                        // the member itself goes to the target's candidate list (one atomic per warp)
-                        const int lane = threadIdx.x & 31, lead = __ffs(hits) - 1;
+                        // the member itself goes to the target's candidate list (one atomic per group of lanes)
+                        const int lead = __ffs(peers) - 1;
                         unsigned base = 0;
-                        if (lane == lead) base = atomicAdd(&a.cand_n[(size_t)inst * kSelTargets + tg], (unsigned)__popc(hits));
-                        base = __shfl_sync(hits, base, lead) + (unsigned)__popc(hits & ((1u << lane) - 1u));
+                        if (lane == lead) base = atomicAdd(&a.cand_n[(size_t)inst * kSelTargets + tg], (unsigned)__popc(peers));
+                        base = __shfl_sync(peers, base, lead) + (unsigned)__popc(peers & ((1u << lane) - 1u));
                         if (base < (unsigned)kSelListCap)
                             reinterpret_cast<typename SelBits<T>::type*>(a.cand)[((size_t)inst * kSelTargets + tg) * kSelListCap + base] =
                                 (typename SelBits<T>::type)sel_bits<T>(x[j]);
