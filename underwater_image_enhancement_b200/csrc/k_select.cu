@@ -183,6 +183,49 @@ __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
     const long long units = a.n / PER;
     const long long stride = (long long)gridDim.x * NT;
     const long long rounds = (units + stride - 1) / stride;     // whole warps stay in the loop
+    using U = typename SelBits<T>::type;
+    __shared__ unsigned s_qkey[NT / 32][64];
+    __shared__ U s_qbits[NT / 32][64];
+    __shared__ uint8_t s_qch[NT / 32][64];
+    const int lane = threadIdx.x & 31;
+    unsigned* qkey = s_qkey[threadIdx.x >> 5];
+    U* qbits = s_qbits[threadIdx.x >> 5];
+    uint8_t* qch = s_qch[threadIdx.x >> 5];
+    int qn = 0;                                                 // warp-uniform
+    // entries 0 .. cnt-1 of the queue, one per lane: histogram of the next digit and, at level 1, the candidate list
+    auto drain = [&](int cnt) {
+        int tg = -1;
+        unsigned sub = 0;
+        U bits = 0;
+        if (lane < cnt) {
+            const unsigned k = qkey[lane];
+            const int c = qch[lane];
+            const unsigned hi = k >> SHIFT;
+            sub = (k >> SUBSHIFT) & SUBMASK;
+            bits = qbits[lane];
+            const int nt = ps.cnt[c];
+            for (int t = 0; t < nt; ++t) {                      // the targets that are on have distinct prefixes: at most one matches
+                const int cand_t = ps.list[c][t];
+                if (ps.pre[cand_t] == hi) tg = cand_t;
+            }
+        }
+        const unsigned valid = __ballot_sync(0xffffffffu, tg >= 0);
+        if (tg >= 0) {
+            const unsigned peers = __match_any_sync(valid, (unsigned)tg);                   // same target
+            const unsigned same = __match_any_sync(peers, sub);                             // ... and same bin: one atomic
+            if ((int)(__ffs(same) - 1) == lane) atomicAdd(gh + (size_t)tg * BINS + sub, (unsigned)__popc(same));
+            if (LEVEL == 1) {
+                // the member itself goes to the target's candidate list (one atomic per target present)
+                const int lead = __ffs(peers) - 1;
+                unsigned base = 0;
+                if (lane == lead) base = atomicAdd(&a.cand_n[(size_t)inst * kSelTargets + tg], (unsigned)__popc(peers));
+                base = __shfl_sync(peers, base, lead) + (unsigned)__popc(peers & ((1u << lane) - 1u));
+                if (base < (unsigned)kSelListCap)
+                    reinterpret_cast<U*>(a.cand)[((size_t)inst * kSelTargets + tg) * kSelListCap + base] = bits;
+            }
+        }
+        __syncwarp();
+    };
     for (long long rd = 0; rd < rounds; ++rd) {
         const long long u = rd * stride + (long long)blockIdx.x * NT + threadIdx.x;
         const bool in = u < units;
@@ -206,37 +249,39 @@ __global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
             if (ka <= 1024u && ps.hot[j % 3][ka] != 0) hot |= 1u << j;
         }
         // A hot value is rare per LANE (the targets' level-A bins hold ~1 % of the data) but not per warp (384 values a
-        // round): the lanes that hold one take this branch alone and meet whoever else is there (__activemask), instead
-        // of all 32 lanes walking every value slot and every target behind warp-wide ballots.
-        if (hot != 0) {
+        // round).  Hot values are first compacted into the warp's queue in shared memory - every lane pushes one of its
+        // own per trip, positions from a ballot - and handled 32 at a time, one per lane.
+        unsigned m = hot;
+        while (true) {
+            const unsigned has = __ballot_sync(0xffffffffu, m != 0);
+            if (has == 0) break;
+            if (m != 0) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1;
+                unsigned kj = 0;
+                U bj = 0;
 #pragma unroll
-            for (int j = 0; j < 3 * PER; ++j) {
-                if (!((hot >> j) & 1u)) continue;
-                const int c = j % 3;
-                const unsigned hi = key[j] >> SHIFT, sub = (key[j] >> SUBSHIFT) & SUBMASK;
-                const int nt = ps.cnt[c];
-#pragma unroll 1
-                for (int t = 0; t < nt; ++t) {
-                    const int tg = ps.list[c][t];
-                    if (ps.pre[tg] != hi) continue;
-                    const int lane = threadIdx.x & 31;
-                    const unsigned peers = __match_any_sync(__activemask(), (unsigned)tg);     // lanes here for the same target
-                    const unsigned same = __match_any_sync(peers, sub);                         // ... and the same bin: one atomic
-                    if ((int)(__ffs(same) - 1) == lane) atomicAdd(gh + (size_t)tg * BINS + sub, (unsigned)__popc(same));
-                    if (LEVEL == 1) {
-                        // the member itself goes to the target's candidate list (one atomic per group of lanes)
-                        const int lead = __ffs(peers) - 1;
-                        unsigned base = 0;
-                        if (lane == lead) base = atomicAdd(&a.cand_n[(size_t)inst * kSelTargets + tg], (unsigned)__popc(peers));
-                        base = __shfl_sync(peers, base, lead) + (unsigned)__popc(peers & ((1u << lane) - 1u));
-                        if (base < (unsigned)kSelListCap)
-                            reinterpret_cast<typename SelBits<T>::type*>(a.cand)[((size_t)inst * kSelTargets + tg) * kSelListCap + base] =
-                                (typename SelBits<T>::type)sel_bits<T>(x[j]);
-                    }
-                }
+                for (int jj = 0; jj < 3 * PER; ++jj)
+                    if (jj == j) { kj = key[jj]; bj = (U)sel_bits<T>(x[jj]); }
+                const int at = qn + __popc(has & ((1u << lane) - 1u));
+                qkey[at] = kj; qbits[at] = bj; qch[at] = (uint8_t)(j % 3);
+            }
+            qn += __popc(has);
+            __syncwarp();
+            if (qn >= 32) {
+                drain(32);
+                // the (at most 31) entries behind the drained ones move to the front
+                const int left = qn - 32;
+                unsigned k2 = 0; U b2 = 0; uint8_t c2 = 0;
+                if (lane < left) { k2 = qkey[32 + lane]; b2 = qbits[32 + lane]; c2 = qch[32 + lane]; }
+                __syncwarp();
+                if (lane < left) { qkey[lane] = k2; qbits[lane] = b2; qch[lane] = c2; }
+                qn = left;
+                __syncwarp();
             }
         }
     }
+    if (qn > 0) drain(qn);
 }
 
 // ---- candidate lists: a target whose level-A bin fitted its list is resolved here, with no further
