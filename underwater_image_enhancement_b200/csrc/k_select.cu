@@ -169,7 +169,7 @@ __device__ __forceinline__ void load12(const double* p, double (&v)[12]) {
 
 // VEC: every thread takes 4 pixels per round (n % 4 == 0, so every instance starts 16-byte aligned)
 template <class T, int LEVEL, bool VEC>
-__global__ void __launch_bounds__(NT) sel_hist_kernel(SelectArgs a) {
+__global__ void __launch_bounds__(NT, 4) sel_hist_kernel(SelectArgs a) {
     __shared__ PassState ps;
     const int inst = blockIdx.y;
     if (!pass_prologue<LEVEL>(a, inst, ps, false)) return;
