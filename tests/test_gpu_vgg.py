@@ -120,3 +120,23 @@ def test_enhance_from_bytes_equals_enhance_of_float_image(cuda_device):
     u = used8.cpu().numpy()
     want = o.vgg_enhance(img.cpu().numpy(), u[0], u[1], u[2], u[3])
     assert np.abs(out8.cpu().numpy() - want).max() <= 1e-6
+
+
+def test_order_statistics_from_byte_bins_and_the_fallback(cuda_device):
+    """uwie_vgg_enhance[_dev] resolves the order statistics in its first pass when a plane has at most one float32 per byte
+    bin round(255 x) (k_vgg.cu: vgg_sel_hist_kernel<0>), else by the three-pass radix selection.  Both must give the oracle's
+    bits (no gamma: exact) for: bytes / 255 divided on the host (exact quotients), divided by torch on the device (its
+    reciprocal multiply is 1 ulp off for some bytes), and a plane where two neighbouring floats share a bin."""
+    import torch
+    frames = np.stack([synth_image(40 + i, 97, 131) for i in range(2)])
+    host = np.ascontiguousarray((frames.astype(np.float32) / 255.0).transpose(0, 3, 1, 2))
+    dev = (torch.from_numpy(frames).cuda().to(torch.float32) / 255.0).permute(0, 3, 1, 2).contiguous()
+    mixed = host.copy()
+    v = mixed[0, 1, 10, 10]
+    mixed[0, 1, 10, 11] = np.nextafter(v, np.float32(2.0))          # same byte bin, another float: plane 1 takes the radix passes
+    lo, hi, om = [3.0, 12.0], [97.0, 88.0], [0.4, 0.7]
+    enh = vgg.DifferentiableEnhancement()
+    for name, x in (("host", torch.from_numpy(host).cuda()), ("device", dev), ("mixed", torch.from_numpy(mixed).cuda())):
+        got = enh(x, {"L_low": torch.tensor(lo), "L_high": torch.tensor(hi), "omega": torch.tensor(om)}).cpu().numpy()
+        want = o.vgg_enhance(x.cpu().numpy(), lo, hi, om, None)
+        assert np.array_equal(got, want), name

@@ -52,15 +52,29 @@ __device__ __forceinline__ float key_value(unsigned k) {
 // PASS 0: histogram of key >> 21 (shared by both targets)
 // PASS 1: per target, keys with key >> 21 == prefix: histogram of (key >> 10) & 2047
 // PASS 2: per target, keys with key >> 10 == prefix: histogram of key & 1023
+// PASS 0 also asks whether the plane is made of bytes - at most one distinct float32 per byte bin round(255 x), which is
+// what imread / 255 (use_trained_model.py:119) and every loader of the reference produce, whichever way the division
+// was rounded - and counts the bins: then the order statistics follow from 256 bins at once (vgg_sel_scan_kernel<0> marks
+// the targets resolved, rank = -1) and passes 1 and 2 return in their first instruction: the plane is read twice (here
+// and by the enhancement), not four times.  x -> round(255 x) is monotone, so the bins are in value order.
+constexpr int kByteHist = 264;              // 256 counts + [256] = "two different values met in one bin, or a value outside" + padding
+constexpr int kByteRows = 2;                // two blocks of [planes][kByteHist]: the counts (cleared to 0), then the bins' float32 bit patterns (cleared to kNoValue)
+constexpr unsigned kNoValue = 0xffffffffu;  // not a value this path accepts (a NaN): what memset 0xFF leaves
 template <int PASS>
 __global__ void __launch_bounds__(NT) vgg_sel_hist_kernel(const float* __restrict__ data, long long n, long long plane_stride,
                                                           int elem_stride, const SelState* __restrict__ state,
-                                                          unsigned* __restrict__ hist) {
+                                                          unsigned* __restrict__ hist, unsigned* __restrict__ bhist) {
     constexpr int BINS = PASS == 2 ? kBinsC : kBinsAB;
     constexpr int NH = PASS == 0 ? 1 : kTargets;
     __shared__ unsigned sh[NH][BINS];
+    __shared__ unsigned sb[PASS == 0 ? 256 : 1];
+    __shared__ unsigned s_rep[PASS == 0 ? 256 : 1];
     const int plane = blockIdx.y;
+    if (PASS > 0 && state[plane * kTargets].rank < 0 && state[plane * kTargets + 1].rank < 0) return;   // resolved from the bytes
     for (int i = threadIdx.x; i < NH * BINS; i += NT) (&sh[0][0])[i] = 0;
+    if (PASS == 0)
+        for (int i = threadIdx.x; i < 256; i += NT) { sb[i] = 0; s_rep[i] = kNoValue; }
+    bool odd = false;                           // this thread met a value that is not a byte
     unsigned pre[kTargets] = {0, 0};
     if (PASS > 0) {
 #pragma unroll
@@ -70,8 +84,19 @@ __global__ void __launch_bounds__(NT) vgg_sel_hist_kernel(const float* __restric
     const float* p = data + (size_t)plane * plane_stride;
     auto visit = [&](float x) {
         const unsigned k = sort_key(x);
-        if (PASS == 0) atomicAdd(&sh[0][k >> 21], 1u);
-        else if (PASS == 1) {
+        if (PASS == 0) {
+            atomicAdd(&sh[0][k >> 21], 1u);
+            const int v = __float2int_rn(__fmul_rn(x, 255.0f));
+            const unsigned bits = __float_as_uint(x);
+            if ((unsigned)v <= 255u) {
+                unsigned rep = s_rep[v];
+                if (rep == kNoValue) { rep = atomicCAS(&s_rep[v], kNoValue, bits); if (rep == kNoValue) rep = bits; }
+                if (rep == bits) atomicAdd(&sb[v], 1u);
+                else odd = true;
+            } else {
+                odd = true;
+            }
+        } else if (PASS == 1) {
 #pragma unroll
             for (int t = 0; t < kTargets; ++t) if ((k >> 21) == pre[t]) atomicAdd(&sh[t][(k >> 10) & 2047u], 1u);
         } else {
@@ -89,17 +114,30 @@ __global__ void __launch_bounds__(NT) vgg_sel_hist_kernel(const float* __restric
         for (long long i = (long long)blockIdx.x * NT + threadIdx.x; i < n; i += (long long)gridDim.x * NT)
             visit(p[i * elem_stride]);
     }
-    __syncthreads();
+    int any_odd = __syncthreads_or(odd);
     unsigned* gh = hist + (size_t)plane * NH * BINS;
     for (int i = threadIdx.x; i < NH * BINS; i += NT) {
         const unsigned v = (&sh[0][0])[i];
         if (v) atomicAdd(&gh[i], v);
     }
+    if (PASS == 0) {
+        unsigned* gb = bhist + (size_t)plane * kByteHist;
+        unsigned* grep = bhist + ((size_t)gridDim.y + plane) * kByteHist;
+        bool clash = false;
+        for (int i = threadIdx.x; i < 256; i += NT)
+            if (sb[i]) {
+                atomicAdd(&gb[i], sb[i]);
+                const unsigned old = atomicCAS(&grep[i], kNoValue, s_rep[i]);          // the plane's value of this bin
+                if (old != kNoValue && old != s_rep[i]) clash = true;
+            }
+        any_odd |= __syncthreads_or(clash);
+        if (any_odd && threadIdx.x == 0) atomicOr(&gb[256], 1u);
+    }
 }
 
 // one block per plane: walk the histogram of each target to the bin holding its rank
 template <int PASS>
-__global__ void __launch_bounds__(NT) vgg_sel_scan_kernel(SelState* state, unsigned* hist) {
+__global__ void __launch_bounds__(NT) vgg_sel_scan_kernel(SelState* state, unsigned* hist, unsigned* bhist) {
     constexpr int BINS = PASS == 2 ? kBinsC : kBinsAB;
     constexpr int NH = PASS == 0 ? 1 : kTargets;
     constexpr int PER = BINS / NT;
@@ -111,7 +149,7 @@ __global__ void __launch_bounds__(NT) vgg_sel_scan_kernel(SelState* state, unsig
         for (int i = 0; i < PER; ++i) s += h[threadIdx.x * PER + i];
         part[threadIdx.x] = s;
         __syncthreads();
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == 0 && state[plane * kTargets + t].rank >= 0) {
             SelState st = state[plane * kTargets + t];
             unsigned long long acc = 0;
             int seg = 0;
@@ -121,6 +159,17 @@ __global__ void __launch_bounds__(NT) vgg_sel_scan_kernel(SelState* state, unsig
             st.rank -= (long long)acc;
             st.prefix = PASS == 0 ? (unsigned)bin : ((st.prefix << (PASS == 1 ? 11 : 10)) | (unsigned)bin);
             if (PASS == 2) st.value = key_value(st.prefix);
+            if (PASS == 0 && bhist[(size_t)plane * kByteHist + 256] == 0) {
+                // a plane of bytes: the order statistic is the value of the bin that holds the rank
+                const unsigned* hb = bhist + (size_t)plane * kByteHist;
+                const unsigned* hrep = bhist + ((size_t)gridDim.x + plane) * kByteHist;
+                const long long rank = st.rank + (long long)acc;           // the rank in the whole plane
+                long long c = 0;
+                int v = 0;
+                for (; v < 255; ++v) { c += hb[v]; if (c > rank) break; }
+                st.value = __uint_as_float(hrep[v]);
+                st.rank = -1;
+            }
             state[plane * kTargets + t] = st;
         }
         __syncthreads();
@@ -351,7 +400,7 @@ __global__ void __launch_bounds__(NT) vgg_preprocess_kernel(const In* __restrict
     }
 }
 
-struct VggLayout { size_t state, prm, hist, total; };
+struct VggLayout { size_t state, prm, hist, bhist, hist_bytes, bhist_bytes, total; };
 VggLayout vgg_layout(int batch) {
     VggLayout L;
     size_t off = 0;
@@ -360,6 +409,9 @@ VggLayout vgg_layout(int batch) {
     L.prm = take((size_t)batch * sizeof(EnhanceParams));
     // the widest use: pass 1 of the selection (planes x targets x 2048 bins); features need batch x 768
     L.hist = take((size_t)batch * 3 * kTargets * kBinsAB * 4);
+    L.hist_bytes = (size_t)batch * 3 * kTargets * kBinsAB * 4;
+    L.bhist_bytes = (size_t)batch * 3 * kByteRows * kByteHist * 4;
+    L.bhist = take(L.bhist_bytes);
     L.total = off;
     return L;
 }
@@ -567,18 +619,21 @@ int uwie_vgg_enhance(const float* img_dev, int batch, int height, int width, con
     SelState* state = (SelState*)(ws + L.state);
     EnhanceParams* prm = (EnhanceParams*)(ws + L.prm);
     unsigned* hist = (unsigned*)(ws + L.hist);
+    unsigned* bhist = (unsigned*)(ws + L.bhist);
     // pageable sources: the runtime stages them before returning, so the vectors may die with this frame
     CUV(cudaMemcpyAsync(state, hs.data(), hs.size() * sizeof(SelState), cudaMemcpyHostToDevice, st));
     CUV(cudaMemcpyAsync(prm, hp.data(), hp.size() * sizeof(EnhanceParams), cudaMemcpyHostToDevice, st));
-    CUV(cudaMemsetAsync(hist, 0, (size_t)batch * 3 * kTargets * kBinsAB * 4, st));
+    CUV(cudaMemsetAsync(hist, 0, L.hist_bytes, st));
+    CUV(cudaMemsetAsync(bhist, 0, L.bhist_bytes / 2, st));
+    CUV(cudaMemsetAsync(reinterpret_cast<char*>(bhist) + L.bhist_bytes / 2, 0xff, L.bhist_bytes / 2, st));
     const int planes = batch * 3;
     const dim3 grid(grid_for(n / 4 + 1), planes);
-    vgg_sel_hist_kernel<0><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
-    vgg_sel_scan_kernel<0><<<planes, NT, 0, st>>>(state, hist);
-    vgg_sel_hist_kernel<1><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
-    vgg_sel_scan_kernel<1><<<planes, NT, 0, st>>>(state, hist);
-    vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
-    vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist);
+    vgg_sel_hist_kernel<0><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist, bhist);
+    vgg_sel_scan_kernel<0><<<planes, NT, 0, st>>>(state, hist, bhist);
+    vgg_sel_hist_kernel<1><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist, bhist);
+    vgg_sel_scan_kernel<1><<<planes, NT, 0, st>>>(state, hist, bhist);
+    vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist, bhist);
+    vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist, bhist);
     vgg_enhance_kernel<<<dim3(grid_for(n / 4 + 1), batch), NT, 0, st>>>(img_dev, out_dev, n, state, prm, omega ? 1 : 0, gamma ? 1 : 0);
     CUV(cudaGetLastError());
     return UWIE_OK;
@@ -596,16 +651,19 @@ int uwie_vgg_enhance_dev(const float* img_dev, int batch, int height, int width,
     SelState* state = (SelState*)(ws + L.state);
     EnhanceParams* prm = (EnhanceParams*)(ws + L.prm);
     unsigned* hist = (unsigned*)(ws + L.hist);
+    unsigned* bhist = (unsigned*)(ws + L.bhist);
     vgg_params_kernel<<<(batch + 127) / 128, 128, 0, st>>>(params_dev, batch, n, clamp_ranges, state, prm, used_dev);
-    CUV(cudaMemsetAsync(hist, 0, (size_t)batch * 3 * kTargets * kBinsAB * 4, st));
+    CUV(cudaMemsetAsync(hist, 0, L.hist_bytes, st));
+    CUV(cudaMemsetAsync(bhist, 0, L.bhist_bytes / 2, st));
+    CUV(cudaMemsetAsync(reinterpret_cast<char*>(bhist) + L.bhist_bytes / 2, 0xff, L.bhist_bytes / 2, st));
     const int planes = batch * 3;
     const dim3 grid(grid_for(n / 4 + 1), planes);
-    vgg_sel_hist_kernel<0><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
-    vgg_sel_scan_kernel<0><<<planes, NT, 0, st>>>(state, hist);
-    vgg_sel_hist_kernel<1><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
-    vgg_sel_scan_kernel<1><<<planes, NT, 0, st>>>(state, hist);
-    vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist);
-    vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist);
+    vgg_sel_hist_kernel<0><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist, bhist);
+    vgg_sel_scan_kernel<0><<<planes, NT, 0, st>>>(state, hist, bhist);
+    vgg_sel_hist_kernel<1><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist, bhist);
+    vgg_sel_scan_kernel<1><<<planes, NT, 0, st>>>(state, hist, bhist);
+    vgg_sel_hist_kernel<2><<<grid, NT, 0, st>>>(img_dev, n, n, 1, state, hist, bhist);
+    vgg_sel_scan_kernel<2><<<planes, NT, 0, st>>>(state, hist, bhist);
     vgg_enhance_kernel<<<dim3(grid_for(n / 4 + 1), batch), NT, 0, st>>>(img_dev, out_dev, n, state, prm, 1, 1);
     CUV(cudaGetLastError());
     return UWIE_OK;
