@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(GNT, GBLOCKS_PER_SM) gf_ab_kernel(GuidedArgs a
             const double var = __dsub_rn(mII, __dmul_rn(mI, mI));
             const double den = __dadd_rn(var, eps);
             // FAST: eps >= 1e-9, so den is normal and |a| < 1e10 (a is 0 or far above the subnormals)
-            const double ra = FAST ? div_rn_normal(cov, den) : __ddiv_rn(cov, den);
+            const double ra = FAST ? div_2ulp_normal(cov, den) : __ddiv_rn(cov, den);
             const double rb = __dsub_rn(mP, __dmul_rn(ra, mI));
             if (base + j < s.outw && s.xs + base + j < a.W) {
                 if (sizeof(AB) == 16) *reinterpret_cast<double2*>(&orow[j]) = make_double2(ra, rb);
