@@ -51,7 +51,7 @@ __device__ __forceinline__ void stage_bytes(const ApplyArgs& a, const Recipe& rc
 // slot of `out`, and apply_kernel continues from them in place (no second conversion, and for the dehaze strategies
 // no second read of the float planes and no second pass through the pre-stretches).
 template <class T>
-__global__ void __launch_bounds__(NT) clahe_lut_kernel(ApplyArgs a) {
+__global__ void __launch_bounds__(NT, 6) clahe_lut_kernel(ApplyArgs a) {
     const int s = blockIdx.y, b = blockIdx.z;
     const Recipe& rc = a.recipes[s];
     if (!rc.clahe || (int)blockIdx.x >= rc.tiles_x * rc.tiles_y) return;
