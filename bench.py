@@ -232,9 +232,12 @@ def stage_alg_bytes(library: str):
         "quadtree_canny": 4,                                  # frame quadrants: 3N * (1 + 1/4 + 1/16 + ...)
         "guided_recover": 3 + nd * rec,                       # frame in, recovered planes out
         "percentile_select": nd * rec,                        # one read of the data being ranked
-        "clahe_tile_luts": n_clahe_dehaze * rec + n_clahe_frame * 3,
-        "clahe_out_hist": 3,
-        "final_apply": nd * rec + (S - nd) * 3 + S * 4,       # stage inputs in, S x (RGB + gray) out
+        # CLAHE strategies: stage input in (recovered planes or frame bytes), Lab bytes out (the hand-off to the apply passes)
+        "clahe_tile_luts": n_clahe_dehaze * rec + n_clahe_frame * 3 + (n_clahe_dehaze + n_clahe_frame) * 3,
+        "clahe_out_hist": 3 + 3,                              # Lab bytes in, CLAHE output bytes out (one strategy)
+        # CLAHE strategies continue from 3 N of Lab (or CLAHE) bytes, the others from their stage input; S x (RGB + gray) out
+        "final_apply": (n_clahe_dehaze + n_clahe_frame) * 3 + (nd - n_clahe_dehaze) * rec
+                       + (S - nd - n_clahe_frame) * 3 + S * 4,
         "score_canny": S * 1,                                 # gray planes in, counts out
     }
 
