@@ -111,8 +111,11 @@ __global__ void __launch_bounds__(NT, 6) clahe_lut_kernel(ApplyArgs a) {
     if (inside) {
         const int gpr = geo.tw >> 2;                       // 4-pixel groups per tile row
         const int groups = gpr * geo.th;
-        for (int i = threadIdx.x; i < groups; i += NT) {
-            const int ly = i / gpr, gx = i - ly * gpr;
+        // (row, group) of a thread's next item without a division per trip: NT groups further on
+        const int step_y = NT / gpr, step_x = NT - step_y * gpr;
+        int ly = threadIdx.x / gpr, gx = threadIdx.x - ly * gpr;
+        for (int i = threadIdx.x; i < groups; i += NT, ly += step_y, gx += step_x) {
+            if (gx >= gpr) { gx -= gpr; ++ly; }
             const size_t p = (size_t)(y0 + ly) * a.W + x0 + 4 * gx;
             uint32_t l0, l1, l2, l3;
             if (!dehaze) {
