@@ -61,12 +61,26 @@ __global__ void __launch_bounds__(256) gf_prep_kernel(GuidedArgs a) {
     const unsigned npix = (unsigned)a.H * a.W;
     const uint8_t* f = a.frames + (size_t)b * npix * 3;
     uint2* gd = a.gd_plane + (size_t)b * npix;
-    for (unsigned i = blockIdx.x * 256 + threadIdx.x; i < npix; i += gridDim.x * 256) {
-        const unsigned r = f[i * 3], g = f[i * 3 + 1], bl = f[i * 3 + 2];
+    auto record = [&](unsigned r, unsigned g, unsigned bl) {
         const unsigned gq = (unsigned)gray_q15(sq[0][r], sq[1][g], sq[2][bl]);
         const float dk = fminf(fminf(sdiv[0][r], sdiv[1][g]), sdiv[2][bl]);
-        gd[i] = make_uint2(r | (g << 8) | (bl << 16) | (gq << 24), __float_as_uint(dk));
+        return make_uint2(r | (g << 8) | (bl << 16) | (gq << 24), __float_as_uint(dk));
+    };
+    // four pixels per thread: three 32-bit loads in, two 128-bit stores out
+    const unsigned groups = ((reinterpret_cast<uintptr_t>(f) & 3) == 0 && (reinterpret_cast<uintptr_t>(gd) & 15) == 0) ? npix / 4 : 0;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(f);
+    for (unsigned i = blockIdx.x * 256 + threadIdx.x; i < groups; i += gridDim.x * 256) {
+        const uint32_t w0 = __ldg(w + 3 * i), w1 = __ldg(w + 3 * i + 1), w2 = __ldg(w + 3 * i + 2);
+        const uint2 p0 = record(w0 & 255, (w0 >> 8) & 255, (w0 >> 16) & 255);
+        const uint2 p1 = record(w0 >> 24, w1 & 255, (w1 >> 8) & 255);
+        const uint2 p2 = record((w1 >> 16) & 255, w1 >> 24, w2 & 255);
+        const uint2 p3 = record((w2 >> 8) & 255, (w2 >> 16) & 255, w2 >> 24);
+        uint4* o = reinterpret_cast<uint4*>(gd + 4 * (size_t)i);
+        o[0] = make_uint4(p0.x, p0.y, p1.x, p1.y);
+        o[1] = make_uint4(p2.x, p2.y, p3.x, p3.y);
     }
+    for (unsigned i = 4 * groups + blockIdx.x * 256 + threadIdx.x; i < npix; i += gridDim.x * 256)
+        gd[i] = record(f[i * 3], f[i * 3 + 1], f[i * 3 + 2]);
 }
 
 template <bool CLIP>
