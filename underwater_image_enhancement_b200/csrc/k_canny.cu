@@ -203,7 +203,9 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
     if (MODE == CANNY_QUADRANTS) {
         const uint8_t* frame = a.frames + (size_t)j.img * npix * 3;
         const CastTables* ct = a.cast + j.img;
-        for (int i = tid; i < 768; i += NT) shist[i] = 0;
+        // the frame's byte tables (colour-cast correction + quantisation) in shared memory: the magnitude tile is not live yet
+        uint8_t* s_curq = sraw + SG_BYTES;
+        for (int i = tid; i < 768; i += NT) { shist[i] = 0; s_curq[i] = (&ct->curq[0][0])[i]; }
         __syncthreads();
         for (int i = tid; i < GH * GL; i += NT) {
             const int ly = i / GL, lx = i - ly * GL;
@@ -211,7 +213,7 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
             const int y = j.y0 + clamp_idx(ry, rows), x = j.x0 + clamp_idx(rx, cols);
             const uint8_t* p = frame + ((size_t)y * a.W + x) * 3;
             const int r0 = p[0], g0 = p[1], b0 = p[2];
-            sg[ly][GPAD + lx] = (uint8_t)gray_q15(ct->curq[0][r0], ct->curq[1][g0], ct->curq[2][b0]);
+            sg[ly][GPAD + lx] = (uint8_t)gray_q15(s_curq[r0], s_curq[256 + g0], s_curq[512 + b0]);
             const bool inner = ly >= 2 && ly < TH + 2 && lx >= 2 && lx < TW + 2 && ry < rows && rx < cols;
             if (inner) {
                 atomicAdd(&shist[r0], 1u);
