@@ -248,16 +248,34 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
         }
     }
 
-    // ---- Sobel by column march: thread = one column of the magnitude tile x one third of its rows.
+    // ---- Sobel by column march: thread = one column of the magnitude tile x one quarter of its rows.
     // h1 = g[x+1] - g[x-1], h2 = g[x-1] + 2 g[x] + g[x+1] per gray row; dx = h1(y-1) + 2 h1(y) + h1(y+1),
     // dy = h2(y+1) - h2(y-1).  Stored: L1 magnitude (0 outside the rectangle) | NMS direction << 12
     // (0 horizontal, 1 vertical, 2 the / diagonal, 3 the \ diagonal; cv2's TG22 fixed-point test).
     {
-        constexpr int CHUNK = (MH + 2) / 3;
-        const int mx = tid % MW, chunk = tid / MW;
-        if (chunk < 3) {
+        // All 256 threads march: column 1 + (tid & 63) of the magnitude tile (its 64 inner columns) x one quarter of its 66
+        // rows.  The two halo columns (0 and 65) are 132 single outputs, taken afterwards by threads 0 .. 131.
+        const int sob_low = a.low;
+        auto encode = [&](int dx, int dy, bool inside) -> int {
+            const int ax = abs(dx), ay = abs(dy);
+            int v = 0;
+            if (inside) {
+                v = ax + ay;
+                if (v > sob_low) {                       // the direction is only read for candidates (m > low): flat rows skip it
+                    const int ys = ay << 15, tg22x = ax * 13573;
+                    int dir;
+                    if (ys < tg22x) dir = 0;
+                    else if (ys > tg22x + (ax << 16)) dir = 1;
+                    else dir = ((dx ^ dy) < 0) ? 2 : 3;
+                    v |= dir << 12;
+                }
+            }
+            return v;
+        };
+        {
+            constexpr int CHUNK = (MH + 3) / 4;
+            const int mx = 1 + (tid & 63), chunk = tid >> 6;
             const int my0 = chunk * CHUNK, my1 = min(my0 + CHUNK, MH);
-            const int sob_low = a.low;
             const int rx = tx0 + mx - 1;
             const bool col_in = rx >= 0 && rx < cols;
             // rows of this chunk that lie inside the rectangle: one unsigned compare per row
@@ -277,21 +295,18 @@ __global__ void __launch_bounds__(NT) canny_tile_kernel(CannyArgs a) {
                 const int h1c = g2 - g0, h2c = g0 + 2 * g1 + g2;
                 const int dx = h1a + 2 * h1b + h1c, dy = h2c - h2a;
                 h1a = h1b; h1b = h1c; h2a = h2b; h2b = h2c;
-                const int ax = abs(dx), ay = abs(dy);
-                int v = 0;
-                if ((unsigned)(my - vlo) < vspan) {
-                    v = ax + ay;
-                    if (v > sob_low) {                   // the direction is only read for candidates (m > low): flat rows skip it
-                        const int ys = ay << 15, tg22x = ax * 13573;
-                        int dir;
-                        if (ys < tg22x) dir = 0;
-                        else if (ys > tg22x + (ax << 16)) dir = 1;
-                        else dir = ((dx ^ dy) < 0) ? 2 : 3;
-                        v |= dir << 12;
-                    }
-                }
-                sm[my][mx] = (uint16_t)v;
+                sm[my][mx] = (uint16_t)encode(dx, dy, (unsigned)(my - vlo) < vspan);
             }
+        }
+        if (tid < 2 * MH) {
+            const int my = tid < MH ? tid : tid - MH, mx = tid < MH ? 0 : MW - 1;
+            const int ry = ty0 + my - 1, rx = tx0 + mx - 1;
+            const uint8_t* p0 = &sg[my][GPAD + mx];
+            const uint8_t* p1 = p0 + GW;
+            const uint8_t* p2 = p1 + GW;
+            const int dx = (p0[2] - p0[0]) + 2 * (p1[2] - p1[0]) + (p2[2] - p2[0]);
+            const int dy = (p2[0] + 2 * p2[1] + p2[2]) - (p0[0] + 2 * p0[1] + p0[2]);
+            sm[my][mx] = (uint16_t)encode(dx, dy, ry >= 0 && ry < rows && rx >= 0 && rx < cols);
         }
     }
     __syncthreads();
