@@ -77,7 +77,10 @@ typedef struct uwie_engine uwie_engine;
 int uwie_version(void);
 const char* uwie_last_error(void);
 
-/* Fill `lib` and `strategies` (room for UWIE_MAX_STRATEGIES) with a preset; returns the count. */
+/* Fill `lib` and `strategies` (room for UWIE_MAX_STRATEGIES) with a preset; returns the count.
+ * UWIE_LIB_SIX: the constants hard-coded in strategy1..6 (six_stadigy.py:230-285) and the default weights of
+ * comprehensive_assessment (quality_assessment.py:229-238); UWIE_LIB_ES: Config.STRATEGIES / Config.QUALITY_WEIGHTS
+ * (config.py:28-85) with the defaults of enhancement_strategies.py:349-474. */
 int uwie_preset(int library_id, uwie_library* lib, uwie_strategy* strategies);
 
 /* Device memory an engine needs for `max_batch` frames of H x W (0 on bad arguments). */

@@ -80,3 +80,25 @@ def test_no_cpu_fallback(native_lib):
     from underwater_image_enhancement_b200.engine import Engine
     with pytest.raises(RuntimeError):
         Engine("six", 64, 64)
+
+
+def test_every_entry_point_cites_the_reference_or_says_it_has_no_counterpart():
+    """include/uwie.h: the comment block above each group of declarations names the reference code the entry points replace
+    (file:line, or the header's own abbreviations ES: / SS: / QA: / FE: / VGG: / UTM:), or says that there is none."""
+    src = open(os.path.join(ROOT, "include", "uwie.h")).read()
+    cite = re.compile(r"(\w+\.py:\d+|\b(ES|SS|QA|FE|VGG|UTM|DLP|MAIN):\d+|NO counterpart|no counterpart)")
+    housekeeping = {"uwie_version", "uwie_last_error", "uwie_workspace_bytes", "uwie_engine_create", "uwie_engine_destroy",
+                    "uwie_engine_check", "uwie_engine_last_launches", "uwie_engine_graph_replays", "uwie_engine_debug",
+                    "uwie_engine_profile", "uwie_engine_profile_read", "uwie_selftest_division", "uwie_engine_host_prepare"}
+    missing = []
+    for m in re.finditer(r"^[a-z_0-9 \*]+?\b(uwie_[a-z0-9_]+)\s*\(", src, flags=re.M):
+        name = m.group(1)
+        if name in housekeeping or name.endswith("_workspace_bytes"):
+            continue
+        # the nearest comment block that ends before this declaration
+        end = src.rfind("*/", 0, m.start())
+        start = src.rfind("/*", 0, end)
+        assert start >= 0 and end > start, name
+        if not cite.search(src[start:end]):
+            missing.append(name)
+    assert not missing, missing
