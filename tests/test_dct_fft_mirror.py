@@ -72,3 +72,30 @@ def test_sizes_of_the_baseline_configs_factor():
     for n in (1920, 1080, 3840, 2160, 1280, 720):
         assert factors(n) is not None and len(factors(n)) <= 14
     assert factors(33) is None and factors(97) is None
+
+
+@pytest.mark.parametrize("h,w", [(12, 30), (45, 8), (9, 25)])
+def test_two_passes_give_cv2_dct_and_the_five_sums(h, w):
+    """Rows in pairs, then columns in pairs (a lone last row / column rides with zeros), as the two kernels do it; the five
+    sums of feature_extraction.py:142-156 from the coefficients."""
+    from scipy.fft import dctn
+    rng = np.random.default_rng(h * 100 + w)
+    g = rng.random((h, w)).astype(np.float32)
+    T = np.empty((h, w), np.float32)
+    for r in range(0, h, 2):
+        a, b = dct_pair(g[r], g[r + 1] if r + 1 < h else np.zeros(w, np.float32))
+        T[r] = a
+        if r + 1 < h:
+            T[r + 1] = b
+    Z = np.empty((h, w), np.float32)
+    for c in range(0, w, 2):
+        a, b = dct_pair(T[:, c], T[:, c + 1] if c + 1 < w else np.zeros(h, np.float32))
+        Z[:, c] = a
+        if c + 1 < w:
+            Z[:, c + 1] = b
+    ref = dctn(g.astype(np.float64), norm="ortho")
+    assert np.abs(Z - ref).max() < 4e-6
+    e, er = Z.astype(np.float64) ** 2, ref ** 2
+    for sl in ((slice(0, h // 4), slice(0, w // 4)), (slice(h // 4, h // 2), slice(w // 4, w // 2)), (slice(h // 2, h), slice(w // 2, w))):
+        assert abs(e[sl].sum() - er[sl].sum()) <= 1e-5 * max(er[sl].sum(), 1e-9) + 1e-9
+    assert abs(e.sum() - er.sum()) <= 1e-5 * er.sum()
