@@ -24,3 +24,27 @@ for lib, seeds in (("six", (0, 1, 2)), ("es", (0, 1))):
     rep[lib] = rows
 json.dump({"what": "oracle/restatement.py against the unmodified reference (oracle/refload.py) at 1920x1080, CPU", "frames": rep},
           open(os.path.join(ROOT, 'profiles', 'r02_oracle_vs_reference_1080p.json'), 'w'), indent=1)
+
+# ---- the 79 features (feature_extraction.py:249-297) on two of the frames of tests/test_gpu_features.py at 1080p; the
+# texture group runs the reference's call sites on the oracle's stand-ins for scikit-image (tests/golden/make_golden_fe.py)
+sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+from make_golden import REF, install_skimage_standin  # noqa: E402
+install_skimage_standin()
+import skimage  # noqa: E402
+skimage.feature.local_binary_pattern = lambda image, P, R, method="default": o.sk_local_binary_pattern_uniform(image, P, R)
+skimage.feature.graycomatrix = lambda image, distances, angles, levels=None, symmetric=False, normed=False: o.sk_graycomatrix(image, levels)
+skimage.feature.graycoprops = o.sk_graycoprops
+sys.path.insert(0, refload.reference_dir())
+import feature_extraction as fe  # noqa: E402
+fe_rows = []
+for s in (21, 22):
+    frame = synth_image(s, 1080, 1920)
+    f = np.asarray(fe.FeatureExtractor.extract_all_features(frame.astype(np.float32) / 255.0), np.float64)
+    g = o.fe_all(frame)
+    fe_rows.append({"seed": s, "identical_values": int((f == g).sum()), "of": 79,
+                    "max_rel_diff": float((np.abs(f - g) / np.maximum(np.abs(f), 1e-12)).max())})
+    print("fe", fe_rows[-1], flush=True)
+path = os.path.join(ROOT, 'profiles', 'r02_oracle_vs_reference_1080p.json')
+doc = json.load(open(path))
+doc["features79"] = fe_rows
+json.dump(doc, open(path, 'w'), indent=1)
