@@ -48,3 +48,36 @@ path = os.path.join(ROOT, 'profiles', 'r02_oracle_vs_reference_1080p.json')
 doc = json.load(open(path))
 doc["features79"] = fe_rows
 json.dump(doc, open(path, 'w'), indent=1)
+
+# ---- the VGG-path pieces (vgg_16_UIE.py:32-128, 435-466; use_trained_model.py:39-46) at 1080p
+import torch  # noqa: E402
+import torchvision.transforms as T  # noqa: E402
+import use_trained_model as utm  # noqa: E402
+import vgg_16_UIE as vggref  # noqa: E402
+enh = vggref.DifferentiableEnhancement().eval()
+pred = object.__new__(utm.EnhancementPredictor)
+pred.input_size = 224
+pred.normalize = T.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])
+vgg_rows = []
+for s, lo, hi, om, ga in ((60, 4.0, 96.0, 0.55, 1.3), (61, 12.0, 88.0, 0.8, 0.9)):
+    frame = synth_image(s, 1080, 1920)
+    img = frame.astype(np.float32) / 255.0
+    t = torch.from_numpy(img).permute(2, 0, 1).unsqueeze(0)
+    def p(x):
+        return torch.tensor([[float(x)]], dtype=torch.float32)
+    with torch.no_grad():
+        full = enh(t, {"L_low": p(lo), "L_high": p(hi), "omega": p(om), "gamma": p(ga)})[0].numpy()
+        nog = enh(t, {"L_low": p(lo), "L_high": p(hi), "omega": p(om)})[0].numpy()
+    x = np.ascontiguousarray(img.transpose(2, 0, 1))[None]
+    o_full = o.vgg_enhance(x, [lo], [hi], [om], [ga])[0]
+    o_nog = o.vgg_enhance(x, [lo], [hi], [om], None)[0]
+    feats = vggref.extract_all_features(img)
+    pre = pred._preprocess_for_vgg(img)[0].numpy()
+    vgg_rows.append({"seed": s, "enhance_no_gamma_identical": bool(np.array_equal(nog, o_nog)),
+                     "enhance_max_abs_diff": float(np.abs(full - o_full).max()),
+                     "features_max_rel_diff": float((np.abs(feats - o.vgg_features(frame)) / np.maximum(np.abs(feats), 1e-12)).max()),
+                     "preprocess_identical": bool(np.array_equal(pre, o.vgg_preprocess(frame, 224)))})
+    print("vgg", vgg_rows[-1], flush=True)
+doc = json.load(open(path))
+doc["vgg_path"] = vgg_rows
+json.dump(doc, open(path, 'w'), indent=1)
